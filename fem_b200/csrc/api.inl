@@ -1,0 +1,246 @@
+// api.inl -- batch-level entry points (included by femgpu.cu)
+
+static int scan_batch(const femgpu_batch *b, uint64_t *n_bases, int *l_max) {
+  if (!b || (b->n_reads && (!b->bases || !b->offsets))) return set_error(FEMGPU_EINVAL, "null batch");
+  uint64_t lm = 0;
+  for (uint32_t i = 0; i < b->n_reads; ++i) {
+    if (b->offsets[i + 1] < b->offsets[i]) return set_error(FEMGPU_EINVAL, "read offsets must be non-decreasing");
+    lm = std::max(lm, b->offsets[i + 1] - b->offsets[i]);
+  }
+  if (b->n_reads && b->offsets[0] != 0) return set_error(FEMGPU_EINVAL, "offsets[0] must be 0");
+  *n_bases = b->n_reads ? b->offsets[b->n_reads] : 0;
+  if (lm > (uint64_t)FEM_MAX_READ_LEN) return set_error(FEMGPU_EINVAL, "read of %llu bases exceeds the supported maximum %d", (unsigned long long)lm, FEM_MAX_READ_LEN);
+  if (b->n_reads > 0x7FFFFFF0u / 2) return set_error(FEMGPU_EINVAL, "too many reads in one batch");
+  *l_max = (int)lm;
+  return 0;
+}
+
+static int stage_batch(femgpu_ctx *c, Slot &s, const femgpu_params *p, const femgpu_batch *b, Plan *pl) {
+  if (!c || !p) return set_error(FEMGPU_EINVAL, "null argument");
+  CU(cudaSetDevice(c->device));
+  uint64_t n_bases = 0;
+  int l_max = 0;
+  TRY(scan_batch(b, &n_bases, &l_max));
+  TRY(make_plan(c, p, l_max, pl));
+  if (pl->seed_smem > c->smem_optin || pl->cand_smem > c->smem_optin)
+    return set_error(FEMGPU_EINVAL, "shared-memory plan too large (seed %zu, cand %zu bytes)", pl->seed_smem, pl->cand_smem);
+  TRY(slot_reserve(c, s, *pl, b->n_reads, n_bases));
+  s.params = *p;
+  s.n_reads = b->n_reads;
+  s.n_bases = n_bases;
+  s.l_max = l_max;
+  memset(&s.stats, 0, sizeof s.stats);
+  s.stats.num_reads = b->n_reads;
+  cudaEventRecord(s.ev[0], s.stream);
+  if (b->n_reads) {
+    CU(cudaMemcpyAsync(s.bases.p, b->bases, n_bases, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.read_off.p, b->offsets, (b->n_reads + 1ull) * 8, cudaMemcpyHostToDevice, s.stream));
+  }
+  return 0;
+}
+
+// per-read `first` array = every other entry of the per read-strand scan
+static int fetch_result(Slot &s, femgpu_result *r) {
+  const uint32_t n = s.n_reads;
+  uint64_t *hf = s.h_first.as<uint64_t>();
+  if (n == 0) {
+    hf[0] = 0;
+  } else {
+    CU(cudaMemcpy2DAsync(hf, 8, s.rs_map_first.p, 16, 8, (size_t)n + 1, cudaMemcpyDeviceToHost, s.stream));
+    if (s.n_maps) {
+      TRY(s.h_maps.reserve(s.n_maps * 16));
+      CU(cudaMemcpyAsync(s.h_maps.p, s.maps.p, s.n_maps * 16, cudaMemcpyDeviceToHost, s.stream));
+    }
+    // infeasible read-strands are rare; count them from the status bytes
+    TRY(s.h_status.reserve(2ull * n));
+    CU(cudaMemcpyAsync(s.h_status.p, s.rs_status.p, 2ull * n, cudaMemcpyDeviceToHost, s.stream));
+  }
+  cudaEventRecord(s.ev[5], s.stream);
+  CU(cudaStreamSynchronize(s.stream));
+  uint64_t mapped = 0, infeasible = 0;
+  const uint8_t *st = s.h_status.as<uint8_t>();
+  for (uint32_t i = 0; i < n; ++i) {
+    mapped += hf[i + 1] > hf[i];
+    infeasible += st[2 * i] == RS_INFEASIBLE || st[2 * i + 1] == RS_INFEASIBLE;
+  }
+  s.stats.num_mapped_reads = mapped;
+  s.stats.num_infeasible_reads = infeasible;
+  float t;
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[1]); s.ms[0] = t;
+  cudaEventElapsedTime(&t, s.ev[1], s.ev[2]); s.ms[1] = t;
+  cudaEventElapsedTime(&t, s.ev[2], s.ev[3]); s.ms[2] = t;
+  cudaEventElapsedTime(&t, s.ev[3], s.ev[4]); s.ms[3] = t;
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[5]); s.ms[4] = t;
+  if (r) {
+    r->first = hf;
+    r->maps = s.h_maps.as<femgpu_mapping>();
+    r->stats = s.stats;
+  }
+  return 0;
+}
+
+extern "C" int femgpu_submit_batch(femgpu_ctx *c, int slot, const femgpu_params *p, const femgpu_batch *b) {
+  if (!c || slot < 0 || slot > 1) return set_error(FEMGPU_EINVAL, "bad context or slot");
+  Slot &s = c->slot[slot];
+  if (s.busy) return set_error(FEMGPU_ESTATE, "slot %d still holds an unfinished batch", slot);
+  Plan pl;
+  TRY(stage_batch(c, s, p, b, &pl));
+  // The candidate stage needs two small device->host handshakes (arena size, big-path plan), so
+  // the kernels of this slot are driven here; the other slot's D2H and the caller's host work
+  // overlap with them because each slot owns its stream.
+  TRY(run_seed_and_candidates(c, s, pl));
+  TRY(run_verify_and_compact(c, s, pl));
+  s.busy = true;
+  c->last_slot = slot;
+  return 0;
+}
+
+extern "C" int femgpu_wait_batch(femgpu_ctx *c, int slot, femgpu_result *r) {
+  if (!c || slot < 0 || slot > 1) return set_error(FEMGPU_EINVAL, "bad context or slot");
+  Slot &s = c->slot[slot];
+  if (!s.busy) return set_error(FEMGPU_ESTATE, "slot %d has no batch in flight", slot);
+  CU(cudaSetDevice(c->device));
+  s.busy = false;
+  return fetch_result(s, r);
+}
+
+extern "C" int femgpu_map_batch(femgpu_ctx *c, const femgpu_params *p, const femgpu_batch *b, femgpu_result *r) {
+  TRY(femgpu_submit_batch(c, 0, p, b));
+  return femgpu_wait_batch(c, 0, r);
+}
+
+// ---- stage-level: candidates only -------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gather_candidates(const uint64_t *cand, const uint64_t *rs_cand_first,
+                                                           const uint32_t *rs_cand_count, const uint64_t *sorted_first,
+                                                           uint32_t n_rs, uint64_t *out) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (rs >= n_rs) return;
+  const uint64_t src = rs_cand_first[rs], dst = sorted_first[rs];
+  const uint32_t n = rs_cand_count[rs];
+  for (uint32_t t = lane; t < n; t += 32) out[dst + t] = cand[src + t];
+}
+
+extern "C" int femgpu_candidates_batch(femgpu_ctx *c, const femgpu_params *p, const femgpu_batch *b, femgpu_candidates *out) {
+  if (!c || !out) return set_error(FEMGPU_EINVAL, "null argument");
+  Slot &s = c->slot[0];
+  if (s.busy) return set_error(FEMGPU_ESTATE, "slot 0 still holds an unfinished batch");
+  Plan pl;
+  TRY(stage_batch(c, s, p, b, &pl));
+  TRY(run_seed_and_candidates(c, s, pl));
+  const uint64_t n_rs = 2ull * s.n_reads;
+  TRY(s.h_cands.reserve((n_rs + 1) * 8 + s.n_cand * 8 + 16));
+  TRY(s.h_before.reserve(n_rs * 4 + 16));
+  TRY(s.h_status.reserve(n_rs + 16));
+  uint64_t *hfirst = s.h_cands.as<uint64_t>();
+  if (n_rs == 0) {
+    hfirst[0] = 0;
+  } else {
+    Counters *dc = s.counters.as<Counters>();
+    TRY(s.rs_cand_sorted_first.reserve((n_rs + 1) * 8));
+    TRY(s.cand_sorted.reserve(s.n_cand * 8 + 16));
+    const unsigned n_blocks = (unsigned)((n_rs + SCAN_BLOCK - 1) / SCAN_BLOCK);
+    k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.rs_cand_count.as<uint32_t>(), n_rs, s.block_sums.as<uint64_t>());
+    k_scan_blocks<<<1, 32, 0, s.stream>>>(s.block_sums.as<uint64_t>(), n_blocks, (uint64_t *)&dc->total_maps);
+    k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.rs_cand_count.as<uint32_t>(), n_rs, s.block_sums.as<uint64_t>(),
+                                                       s.rs_cand_sorted_first.as<uint64_t>(), (uint64_t *)&dc->total_maps);
+    k_gather_candidates<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(s.cand.as<uint64_t>(), s.rs_cand_first.as<uint64_t>(),
+                                                                        s.rs_cand_count.as<uint32_t>(), s.rs_cand_sorted_first.as<uint64_t>(),
+                                                                        (uint32_t)n_rs, s.cand_sorted.as<uint64_t>());
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(hfirst, s.rs_cand_sorted_first.p, (n_rs + 1) * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (s.n_cand) CU(cudaMemcpyAsync(hfirst + n_rs + 1, s.cand_sorted.p, s.n_cand * 8, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(s.h_before.p, s.rs_before.p, n_rs * 4, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(s.h_status.p, s.rs_status.p, n_rs, cudaMemcpyDeviceToHost, s.stream));
+  }
+  CU(cudaStreamSynchronize(s.stream));
+  out->first = hfirst;
+  out->cands = hfirst + n_rs + 1;
+  out->before = s.h_before.as<uint32_t>();
+  out->status = s.h_status.as<uint8_t>();
+  return 0;
+}
+
+// ---- measurement hooks -----------------------------------------------------------------------------
+extern "C" int femgpu_last_timings(femgpu_ctx *c, float ms[5], uint32_t *n_launches) {
+  if (!c) return set_error(FEMGPU_EINVAL, "null context");
+  const Slot &s = c->slot[c->last_slot];
+  if (ms) memcpy(ms, s.ms, sizeof s.ms);
+  if (n_launches) *n_launches = s.n_launches;
+  return 0;
+}
+
+extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[4]) {
+  if (!c) return set_error(FEMGPU_EINVAL, "null context");
+  Slot &s = c->slot[c->last_slot];
+  if (s.busy) return set_error(FEMGPU_ESTATE, "slot busy");
+  CU(cudaSetDevice(c->device));
+  Plan pl;
+  TRY(make_plan(c, &s.params, s.l_max, &pl));
+  cudaEventRecord(s.ev[0], s.stream);
+  TRY(run_seed_and_candidates(c, s, pl));
+  TRY(run_verify_and_compact(c, s, pl));
+  CU(cudaStreamSynchronize(s.stream));
+  float t;
+  if (ms_stage)
+    for (int i = 0; i < 4; ++i) { cudaEventElapsedTime(&t, s.ev[i], s.ev[i + 1]); ms_stage[i] = t; }
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[4]);
+  if (ms_total) *ms_total = t;
+  return 0;
+}
+
+// ---- host: the reference's per-read mapping order ----------------------------------------------------
+// Key and algorithm of src/align.c:53-57 + klib's radix sort (src/ksort.h:98-151): <= 64 records
+// insertion sort (stable), otherwise an in-place MSD byte-wise "American flag" permutation whose
+// tie order for equal keys depends on the cycle-leader walk, so it is reproduced step for step.
+namespace {
+inline uint64_t map_key(const femgpu_mapping &m) {
+  return ((uint64_t)m.edit_distance << 60) | ((uint64_t)m.direction << 59) |
+         (m.candidate_position + (uint64_t)(int64_t)m.end_position_offset);
+}
+void map_insertion_sort(femgpu_mapping *b, femgpu_mapping *e) {
+  for (femgpu_mapping *i = b + 1; i < e; ++i) {
+    if (map_key(*i) >= map_key(*(i - 1))) continue;
+    const femgpu_mapping t = *i;
+    const uint64_t kt = map_key(t);
+    femgpu_mapping *j = i;
+    for (; j > b && kt < map_key(*(j - 1)); --j) *j = *(j - 1);
+    *j = t;
+  }
+}
+void map_flag_sort(femgpu_mapping *beg, femgpu_mapping *end, int shift) {
+  struct Bucket { femgpu_mapping *head, *tail; } bk[256];
+  size_t hist[256] = {0};
+  for (femgpu_mapping *i = beg; i != end; ++i) ++hist[(map_key(*i) >> shift) & 255];
+  femgpu_mapping *p = beg;
+  for (int d = 0; d < 256; ++d) { bk[d].head = p; p += hist[d]; bk[d].tail = p; }
+  for (int d = 0; d < 256;) {
+    Bucket &cur = bk[d];
+    if (cur.head == cur.tail) { ++d; continue; }
+    int dest = (int)((map_key(*cur.head) >> shift) & 255);
+    if (dest == d) { ++cur.head; continue; }
+    femgpu_mapping moving = *cur.head;
+    while (dest != d) { // push `moving` into its bucket, pick up the record it displaces
+      std::swap(moving, *bk[dest].head);
+      ++bk[dest].head;
+      dest = (int)((map_key(moving) >> shift) & 255);
+    }
+    *cur.head++ = moving;
+  }
+  if (shift == 0) return;
+  const int next = shift > 8 ? shift - 8 : 0;
+  femgpu_mapping *b = beg;
+  for (int d = 0; d < 256; ++d) {
+    femgpu_mapping *e = bk[d].tail;
+    if (e - b > 64) map_flag_sort(b, e, next);
+    else if (e - b > 1) map_insertion_sort(b, e);
+    b = e;
+  }
+}
+} // namespace
+
+extern "C" void femgpu_sort_mappings(femgpu_mapping *maps, size_t n) {
+  if (!maps || n < 2) return;
+  if (n <= 64) map_insertion_sort(maps, maps + n);
+  else map_flag_sort(maps, maps + n, 56);
+}

@@ -1,0 +1,219 @@
+// femgpu.cu -- C-ABI implementation (include/femgpu.h): context, resident data, batch pipeline.
+//
+// One context per GPU.  Per batch ("slot", two of them for double buffering) the pipeline is
+//   H2D(bases, offsets) -> k_seed -> k_cand [-> k_cand_big] -> k_verify -> scan -> k_compact -> D2H
+// on the slot's own stream.  All device buffers are grow-only and reused across batches.
+#include "../../include/femgpu.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "k_cand.cuh"
+#include "k_seed.cuh"
+#include "k_verify.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+static int set_error(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t err__ = (call);                                                                    \
+    if (err__ != cudaSuccess)                                                                      \
+      return set_error(err__ == cudaErrorMemoryAllocation ? FEMGPU_ENOMEM : FEMGPU_ECUDA,          \
+                       "%s failed: %s (%s:%d)", #call, cudaGetErrorString(err__), __FILE__, __LINE__); \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// grow-only buffers
+// ------------------------------------------------------------------------------------------------
+struct DBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  int reserve(size_t need) {
+    if (need <= bytes) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    size_t want = need + need / 4 + 256;
+    if (cudaMalloc(&p, want) != cudaSuccess) {
+      cudaGetLastError();
+      want = need;
+      if (cudaMalloc(&p, want) != cudaSuccess) {
+        cudaGetLastError();
+        p = nullptr;
+        return set_error(FEMGPU_ENOMEM, "cudaMalloc of %zu bytes failed", need);
+      }
+    }
+    bytes = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  template <class T> T *as() const { return static_cast<T *>(p); }
+};
+struct HBuf { // pinned host memory
+  void *p = nullptr;
+  size_t bytes = 0;
+  int reserve(size_t need) {
+    if (need <= bytes) return 0;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    bytes = 0;
+    size_t want = need + need / 4 + 256;
+    if (cudaMallocHost(&p, want) != cudaSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+      return set_error(FEMGPU_ENOMEM, "cudaMallocHost of %zu bytes failed", want);
+    }
+    bytes = want;
+    return 0;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+  template <class T> T *as() const { return static_cast<T *>(p); }
+};
+#define TRY(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+// counters shared between kernels and host (one small device block per slot)
+struct Counters {
+  unsigned long long cand_count;
+  unsigned long long total_before;
+  unsigned long long total_maps;
+  uint32_t overflow_count;
+  int error_flag;
+};
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+  // inputs / per read-strand state
+  DBuf bases, read_off, codes, rs_status, rs_before, rs_max_f, rs_sum_f;
+  DBuf seed_begin, seed_freq, seed_start;
+  DBuf rs_cand_first, rs_cand_count, rs_map_count, rs_map_first, block_sums;
+  DBuf cand, cand_rs, result, maps, overflow_list, counters;
+  DBuf big_list, big_off, big_S, big_A, scratch;
+  DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
+  HBuf h_counters, h_first, h_maps, h_overflow, h_plan, h_cands, h_before, h_status;
+  uint64_t cand_cap = 0;
+  // state of the batch in flight
+  bool busy = false;
+  femgpu_params params{};
+  uint32_t n_reads = 0;
+  uint64_t n_bases = 0;
+  int l_max = 0;
+  uint64_t n_cand = 0, n_maps = 0;
+  femgpu_stats stats{};
+  float ms[5] = {0, 0, 0, 0, 0};
+  uint32_t n_launches = 0;
+};
+
+struct femgpu_ctx {
+  int device = 0;
+  int sm_count = 0;
+  size_t smem_optin = 0;
+  // index
+  DBuf lut, occ;
+  uint64_t n_occ = 0;
+  int idx_k = 0, idx_step = 0;
+  // reference
+  DBuf ref2, refn, rec_base, rec_len;
+  uint32_t n_rec = 0;
+  uint64_t ref_total = 0;
+  bool ref_has_n = false;
+  // options
+  int64_t scratch_limit_bytes = 8ll << 30;
+  int64_t arena_candidates = 0; // 0 = automatic
+  uint32_t sort_capacity = 1024, acc_capacity = 256;
+  int l2_persist_lut = 1;
+  Slot slot[2];
+  int last_slot = 0;
+};
+
+// ------------------------------------------------------------------------------------------------
+// life cycle
+// ------------------------------------------------------------------------------------------------
+extern "C" int femgpu_abi_version(void) { return FEMGPU_ABI_VERSION; }
+
+extern "C" int femgpu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" const char *femgpu_last_error(void) { return g_last_error.c_str(); }
+
+extern "C" femgpu_ctx *femgpu_create(int device) {
+  int n = femgpu_device_count();
+  if (n <= 0) { set_error(FEMGPU_ENODEV, "no CUDA device available (this library has no CPU fallback)"); return nullptr; }
+  if (device < 0 || device >= n) { set_error(FEMGPU_EINVAL, "device %d out of range (0..%d)", device, n - 1); return nullptr; }
+  if (cudaSetDevice(device) != cudaSuccess) { set_error(FEMGPU_ECUDA, "cudaSetDevice(%d) failed", device); return nullptr; }
+  femgpu_ctx *c = new femgpu_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  c->sm_count = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+  for (auto &s : c->slot) {
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
+      set_error(FEMGPU_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
+      delete c;
+      return nullptr;
+    }
+    for (auto &e : s.ev) cudaEventCreate(&e);
+  }
+  return c;
+}
+
+static void slot_release(Slot &s) {
+  DBuf *d[] = {&s.bases, &s.read_off, &s.codes, &s.rs_status, &s.rs_before, &s.rs_max_f, &s.rs_sum_f, &s.seed_begin,
+               &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
+               &s.block_sums, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
+               &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.cand_sorted, &s.rs_cand_sorted_first};
+  for (auto *b : d) b->release();
+  HBuf *h[] = {&s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
+  for (auto *b : h) b->release();
+  for (auto &e : s.ev) if (e) cudaEventDestroy(e);
+  if (s.stream) cudaStreamDestroy(s.stream);
+}
+
+extern "C" void femgpu_destroy(femgpu_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (auto &s : c->slot) slot_release(s);
+  c->lut.release(); c->occ.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release();
+  delete c;
+}
+
+extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) {
+  if (!c || !key) return set_error(FEMGPU_EINVAL, "null argument");
+  std::string k(key);
+  if (k == "scratch_limit_bytes" && value > 0) c->scratch_limit_bytes = value;
+  else if (k == "arena_candidates" && value >= 0) c->arena_candidates = value;
+  else if (k == "sort_capacity" && value >= 32 && value <= 8192 && (value & (value - 1)) == 0) c->sort_capacity = (uint32_t)value;
+  else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
+  else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
+  else return set_error(FEMGPU_EINVAL, "unknown option or bad value: %s=%lld", key, (long long)value);
+  return 0;
+}
+
+extern "C" int femgpu_index_k(const femgpu_ctx *c) { return c ? c->idx_k : 0; }
+extern "C" int femgpu_index_step(const femgpu_ctx *c) { return c ? c->idx_step : 0; }
+
+#include "upload.inl"
+#include "pipeline.inl"
+#include "api.inl"

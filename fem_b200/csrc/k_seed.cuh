@@ -1,0 +1,161 @@
+// k_seed.cuh -- K1: per read-strand base coding, q-gram hashing, lookup-table frequency gather
+// and per-group optimal seed selection.  One warp per read-strand.
+//
+// Restates, in a warp-parallel form, src/sequence_batch.h:90-98 (reverse complement),
+// src/utils.h:83-117 (hashing), src/filter.c:162-204 (feasibility checks, per-group seed tables,
+// DP of src/filter.c:3-43 and the frequency sort).
+//
+// The DP  M[r][c] = min(M[r][c-1], M[r-1][c] + f[c+(r-1)s-1])  (seed taken only when strictly
+// cheaper) is a prefix minimum along c with "left-most achiever wins" tie breaking; each row is
+// one warp scan over (value, column) pairs.  Only the arg-min column per cell is kept (uint16) for
+// the traceback of src/filter.c:30-41.
+#pragma once
+#include "common.cuh"
+
+struct SeedArgs {
+  const char *bases;          // batch bases, reads back to back
+  const uint64_t *read_off;   // n_reads + 1
+  uint32_t n_reads;
+  const uint32_t *lut;
+  uint32_t inf;               // (uint32) occurrence_table_size: the DP's "infinity" (filter.c:9)
+  int k, step, e, a, Q, s;
+  int n_words_max, ns_max, w_max; // shared-memory plan for the longest read of the batch
+  uint8_t *codes;             // out: 2 * total_bases; strand d of read i at 2*off[i] + d*len
+  uint8_t *rs_status;         // out: per read-strand
+  uint32_t *rs_before;        // out: DP minimum summed over groups (filter.c:202)
+  uint32_t *rs_max_f;         // out: max over groups of the selected seeds' total frequency
+  uint32_t *rs_sum_f;         // out: sum over groups of the same (saturating)
+  uint32_t *seed_begin;       // out: [rs*step+g][Q] first occurrence index, frequency order
+  uint32_t *seed_freq;
+  uint32_t *seed_start;       // read offset of the seed
+  unsigned long long *total_before; // out: batch-wide sum of rs_before
+};
+
+__host__ __device__ inline size_t seed_smem_words_per_warp(int n_words_max, int ns_max, int w_max, int Q) {
+  // packed read words + freq + begin + DP row + arg-min table (uint16 pairs)
+  return (size_t)n_words_max + 2 * (size_t)ns_max + (size_t)(w_max + 1) + ((size_t)Q * w_max + 1) / 2;
+}
+
+__global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
+  extern __shared__ uint32_t smem_seed[];
+  const uint32_t lane = lane_id();
+  const uint32_t warp_in_block = threadIdx.x >> 5;
+  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp_in_block;
+  if (rs >= 2ull * A.n_reads) return;
+  const size_t per_warp = seed_smem_words_per_warp(A.n_words_max, A.ns_max, A.w_max, A.Q);
+  uint32_t *pw = smem_seed + warp_in_block * per_warp;      // 2-bit packed read, big-endian in word
+  uint32_t *sm_freq = pw + A.n_words_max;
+  uint32_t *sm_begin = sm_freq + A.ns_max;
+  uint32_t *m_row = sm_begin + A.ns_max;                    // DP row, columns 0..W
+  uint16_t *amin = reinterpret_cast<uint16_t *>(m_row + A.w_max + 1); // [Q][w_max]
+
+  const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
+  const uint64_t off = A.read_off[read];
+  const int l = (int)(A.read_off[read + 1] - off);
+  const int k = A.k, step = A.step, Q = A.Q, s = A.s;
+  const int n_s = l - k + 1;
+  uint8_t *codes = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
+
+  // ---- base codes (strand oriented), 2-bit packing, ambiguous-base count --------------------
+  int amb = 0;
+  const int n_words = (l + 15) / 16 + 1;
+  for (int base = 0; base < n_words * 16; base += 32) {
+    const int i = base + (int)lane;
+    uint32_t c = 0, valid = i < l;
+    if (valid) {
+      c = fem_base_code((unsigned char)(dir ? A.bases[off + (uint64_t)(l - 1 - i)] : A.bases[off + (uint64_t)i]));
+      if (dir && c < 4) c = 3u - c; // 3 ^ code; ambiguous stays ambiguous (-> 'N')
+      codes[i] = (uint8_t)c;
+    }
+    amb += __popc(__ballot_sync(0xffffffffu, valid && c == 4 && i >= k)); // only incoming bases, utils.h:113
+    uint32_t v = (valid && c < 4) ? c << (30 - 2 * (i & 15)) : 0u;         // ambiguous hashed as A
+    v |= __shfl_xor_sync(0xffffffffu, v, 8);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    if ((lane & 15) == 0 && (i >> 4) < n_words) pw[i >> 4] = v;
+  }
+  __syncwarp();
+
+  uint8_t status = RS_OK;
+  if (n_s <= 0) status = RS_INFEASIBLE;                  // reference: assert, filter.c:167
+  else if (Q > n_s / step) status = RS_EMPTY;            // filter.c:168-172
+  else if (amb > A.e) status = RS_EMPTY;                 // filter.c:180-182
+  else if ((n_s - (step - 1)) / step < Q * s) status = RS_INFEASIBLE; // DP table would be < 2 wide
+  uint32_t before = 0, max_f = 0, sum_f = 0;
+
+  if (status == RS_OK) {
+    // ---- hashes and lookup-table gathers (two adjacent uint32 per q-gram) --------------------
+    const uint32_t mask = (uint32_t)((1ull << (2 * k)) - 1);
+    for (int p = (int)lane; p < n_s; p += 32) {
+      const uint64_t x = ((uint64_t)pw[p >> 4] << 32) | pw[(p >> 4) + 1];
+      const uint32_t h = (uint32_t)(x >> (64 - 2 * (p & 15) - 2 * k)) & mask;
+      const uint32_t b = __ldg(A.lut + h), e2 = __ldg(A.lut + h + 1);
+      sm_begin[p] = b;
+      sm_freq[p] = e2 - b;
+    }
+    __syncwarp();
+
+    for (int g = 0; g < step && status == RS_OK; ++g) {
+      const int n_g = (n_s - g) / step;
+      const int W = n_g - Q * s + 1; // real columns 1..W (>= 1 by the feasibility check)
+      for (int c = (int)lane; c <= W; c += 32) m_row[c] = 0; // row 0 (column 0 unused)
+      __syncwarp();
+      for (int r = 1; r <= Q; ++r) {
+        uint32_t carry_v = A.inf, carry_i = 0; // M[r][0] = "infinity", stop marker
+        for (int c0 = 1; c0 <= W; c0 += 32) {
+          const int c = c0 + (int)lane;
+          const bool valid = c <= W;
+          uint32_t v = 0xFFFFFFFFu, idx = (uint32_t)c;
+          if (valid) v = m_row[c] + sm_freq[g + (c + (r - 1) * s - 1) * step];
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t ov = __shfl_up_sync(0xffffffffu, v, d), oi = __shfl_up_sync(0xffffffffu, idx, d);
+            if ((int)lane >= d && ov <= v) { v = ov; idx = oi; }
+          }
+          if (carry_v <= v) { v = carry_v; idx = carry_i; }
+          if (valid) { m_row[c] = v; amin[(r - 1) * A.w_max + (c - 1)] = (uint16_t)idx; }
+          const int last = min(31, W - c0);
+          carry_v = __shfl_sync(0xffffffffu, v, last);
+          carry_i = __shfl_sync(0xffffffffu, idx, last);
+        }
+        __syncwarp();
+      }
+      before += m_row[W];
+      // ---- traceback (filter.c:30-41): lane i keeps the i-th seed found (right-most first) ----
+      int c = W, my_pos = -1;
+      for (int r = Q; r >= 1; --r) {
+        c = amin[(r - 1) * A.w_max + (c - 1)];
+        if (c == 0) { status = RS_INFEASIBLE; break; } // fewer than Q seeds: reference UB
+        if ((int)lane == Q - r) my_pos = g + (c + (r - 1) * s - 1) * step;
+      }
+      if (status != RS_OK) break;
+      // ---- stable ascending sort by frequency (filter.c:204) ------------------------
+      const uint32_t f = my_pos >= 0 ? sm_freq[my_pos] : 0xFFFFFFFFu;
+      int rank = 0;
+      uint32_t tot = 0;
+      for (int j = 0; j < Q; ++j) {
+        const uint32_t fj = __shfl_sync(0xffffffffu, f, j);
+        rank += (fj < f) || (fj == f && j < (int)lane);
+        tot += fj;
+      }
+      if ((int)lane < Q) {
+        const size_t o = ((size_t)rs * step + g) * Q + rank;
+        A.seed_begin[o] = sm_begin[my_pos];
+        A.seed_freq[o] = f;
+        A.seed_start[o] = (uint32_t)my_pos;
+      }
+      max_f = max(max_f, tot);
+      sum_f = (sum_f + tot < sum_f) ? 0xFFFFFFFFu : sum_f + tot;
+      __syncwarp();
+    }
+    if (status != RS_OK) before = 0;
+  }
+  if (lane == 0) {
+    A.rs_status[rs] = status;
+    A.rs_before[rs] = before;
+    A.rs_max_f[rs] = max_f;
+    A.rs_sum_f[rs] = sum_f;
+    if (before) atomicAdd(A.total_before, (unsigned long long)before);
+  }
+}

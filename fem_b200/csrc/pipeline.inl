@@ -1,0 +1,290 @@
+// pipeline.inl -- the per-batch device pipeline (included by femgpu.cu)
+
+struct Plan { // derived from params + the batch
+  int k, step, e, a, Q, s;
+  int l_max, n_words_max, ns_max, w_max;
+  size_t seed_smem;   // bytes per block of k_seed
+  size_t cand_smem;   // bytes per block of k_cand
+};
+
+static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
+  if (!c->n_occ && !c->lut.p) return set_error(FEMGPU_ESTATE, "index not uploaded");
+  if (!c->n_rec) return set_error(FEMGPU_ESTATE, "reference not uploaded");
+  pl->k = p->k > 0 ? p->k : c->idx_k;
+  pl->step = p->step > 0 ? p->step : c->idx_step;
+  pl->e = p->e;
+  pl->a = p->a;
+  if (pl->e < 0 || pl->e > 7) return set_error(FEMGPU_EINVAL, "Wrong error threshold.");          // src/FEM_map.c:30
+  if (pl->a < 0 || pl->a > 2) return set_error(FEMGPU_EINVAL, "Wrong number of additional q-grams."); // :38
+  // the lookup table is addressed by 2k-bit hashes: a seeding k other than the index's would
+  // read out of bounds when larger, and is only meaningful when equal
+  if (pl->k != c->idx_k) return set_error(FEMGPU_EINVAL, "seeding k=%d differs from the index's k=%d", pl->k, c->idx_k);
+  if (pl->step < 1 || pl->step > 64) return set_error(FEMGPU_EINVAL, "bad step %d", pl->step);
+  if (l_max > FEM_MAX_READ_LEN) return set_error(FEMGPU_EINVAL, "read of %d bases exceeds the supported maximum %d", l_max, FEM_MAX_READ_LEN);
+  pl->Q = pl->e + 1 + pl->a;
+  pl->s = pl->k / pl->step + (pl->k % pl->step > 0);
+  pl->l_max = std::max(l_max, 1);
+  pl->n_words_max = (pl->l_max + 15) / 16 + 1;
+  pl->ns_max = std::max(pl->l_max - pl->k + 1, 1);
+  pl->w_max = pl->ns_max / pl->step + 1;
+  pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q) * 4; // 4 warps
+  pl->cand_smem = (size_t)4 * (c->sort_capacity + c->acc_capacity) * 8;
+  return 0;
+}
+
+static int slot_reserve(femgpu_ctx *c, Slot &s, const Plan &pl, uint32_t n_reads, uint64_t n_bases) {
+  const uint64_t n_rs = 2ull * n_reads;
+  const uint64_t n_task = n_rs * pl.step;
+  TRY(s.bases.reserve(n_bases + 16));
+  TRY(s.read_off.reserve((n_reads + 1ull) * 8));
+  TRY(s.codes.reserve(2 * n_bases + 16));
+  TRY(s.rs_status.reserve(n_rs + 16));
+  TRY(s.rs_before.reserve(n_rs * 4 + 16));
+  TRY(s.rs_max_f.reserve(n_rs * 4 + 16));
+  TRY(s.rs_sum_f.reserve(n_rs * 4 + 16));
+  TRY(s.seed_begin.reserve(n_task * pl.Q * 4 + 16));
+  TRY(s.seed_freq.reserve(n_task * pl.Q * 4 + 16));
+  TRY(s.seed_start.reserve(n_task * pl.Q * 4 + 16));
+  TRY(s.rs_cand_first.reserve(n_rs * 8 + 16));
+  TRY(s.rs_cand_count.reserve(n_rs * 4 + 16));
+  TRY(s.rs_map_count.reserve(n_rs * 4 + 16));
+  TRY(s.rs_map_first.reserve((n_rs + 1) * 8));
+  TRY(s.block_sums.reserve((n_rs / SCAN_BLOCK + 2) * 8));
+  TRY(s.overflow_list.reserve(n_rs * 4 + 16));
+  TRY(s.counters.reserve(sizeof(Counters)));
+  TRY(s.h_counters.reserve(sizeof(Counters)));
+  TRY(s.h_first.reserve((n_reads + 1ull) * 8));
+  uint64_t want = c->arena_candidates > 0 ? (uint64_t)c->arena_candidates : std::max<uint64_t>(1u << 20, 16ull * n_reads);
+  if (want > s.cand_cap) {
+    TRY(s.cand.reserve(want * 8));
+    TRY(s.cand_rs.reserve(want * 4));
+    TRY(s.result.reserve(want * 4));
+    s.cand_cap = want;
+  }
+  return 0;
+}
+
+static int grow_arena(Slot &s) {
+  const uint64_t want = s.cand_cap * 2;
+  s.cand_cap = 0;
+  TRY(s.cand.reserve(want * 8));
+  TRY(s.cand_rs.reserve(want * 4));
+  TRY(s.result.reserve(want * 4));
+  s.cand_cap = want;
+  return 0;
+}
+
+__global__ void k_gather_u32(const uint32_t *src, const uint32_t *idx, uint32_t n, uint32_t *dst) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx[i]];
+}
+
+static int read_counters(Slot &s, Counters *out) {
+  CU(cudaMemcpyAsync(s.h_counters.p, s.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
+  *out = *s.h_counters.as<Counters>();
+  return 0;
+}
+
+// k_seed .. candidates resident in the arena.  Records events 1 (after seed) and 2 (after cand).
+static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
+  const uint32_t n_reads = s.n_reads;
+  const uint64_t n_rs = 2ull * n_reads;
+  s.n_launches = 0;
+  CU(cudaMemsetAsync(s.counters.p, 0, sizeof(Counters), s.stream));
+  if (n_reads == 0) {
+    s.n_cand = 0;
+    cudaEventRecord(s.ev[1], s.stream);
+    cudaEventRecord(s.ev[2], s.stream);
+    return 0;
+  }
+  Counters *dc = s.counters.as<Counters>();
+  SeedArgs sa;
+  sa.bases = s.bases.as<char>();
+  sa.read_off = s.read_off.as<uint64_t>();
+  sa.n_reads = n_reads;
+  sa.lut = c->lut.as<uint32_t>();
+  sa.inf = (uint32_t)c->n_occ;
+  sa.k = pl.k; sa.step = pl.step; sa.e = pl.e; sa.a = pl.a; sa.Q = pl.Q; sa.s = pl.s;
+  sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
+  sa.codes = s.codes.as<uint8_t>();
+  sa.rs_status = s.rs_status.as<uint8_t>();
+  sa.rs_before = s.rs_before.as<uint32_t>();
+  sa.rs_max_f = s.rs_max_f.as<uint32_t>();
+  sa.rs_sum_f = s.rs_sum_f.as<uint32_t>();
+  sa.seed_begin = s.seed_begin.as<uint32_t>();
+  sa.seed_freq = s.seed_freq.as<uint32_t>();
+  sa.seed_start = s.seed_start.as<uint32_t>();
+  sa.total_before = &dc->total_before;
+  if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
+  k_seed<<<(unsigned)((n_rs + 3) / 4), 128, pl.seed_smem, s.stream>>>(sa);
+  ++s.n_launches;
+  CU(cudaGetLastError());
+  cudaEventRecord(s.ev[1], s.stream);
+
+  CandArgs ca;
+  memset(&ca, 0, sizeof ca);
+  ca.occ = c->occ.as<uint64_t>();
+  ca.seed_begin = sa.seed_begin; ca.seed_freq = sa.seed_freq; ca.seed_start = sa.seed_start;
+  ca.rs_status = sa.rs_status;
+  ca.read_off = sa.read_off;
+  ca.rec_len = c->rec_len.as<uint32_t>();
+  ca.n_rs = (uint32_t)n_rs;
+  ca.step = pl.step; ca.e = pl.e; ca.a = pl.a; ca.Q = pl.Q;
+  ca.cand_count = &dc->cand_count;
+  ca.rs_cand_first = s.rs_cand_first.as<uint64_t>();
+  ca.rs_cand_count = s.rs_cand_count.as<uint32_t>();
+  ca.overflow_list = s.overflow_list.as<uint32_t>();
+  ca.overflow_count = &dc->overflow_count;
+  ca.error_flag = &dc->error_flag;
+  ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
+  if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
+
+  Counters hc;
+  for (int attempt = 0;; ++attempt) {
+    if (attempt > 12) return set_error(FEMGPU_ELIMIT, "candidate arena keeps overflowing");
+    ca.cand = s.cand.as<uint64_t>();
+    ca.cand_rs = s.cand_rs.as<uint32_t>();
+    ca.cand_cap = s.cand_cap;
+    k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
+    ++s.n_launches;
+    CU(cudaGetLastError());
+    TRY(read_counters(s, &hc));
+    bool arena_full = hc.error_flag == 1;
+    if (!arena_full && hc.overflow_count) {
+      // ---- big path: plan scratch slices on the host, run in rounds within the scratch limit ----
+      const uint32_t n_over = hc.overflow_count;
+      TRY(s.h_overflow.reserve((size_t)n_over * 4));
+      CU(cudaMemcpyAsync(s.h_overflow.p, s.overflow_list.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaStreamSynchronize(s.stream));
+      const uint32_t *ol = s.h_overflow.as<uint32_t>();
+      std::vector<uint32_t> order(ol, ol + n_over);
+      std::sort(order.begin(), order.end()); // deterministic processing order
+      // frequencies of exactly those read-strands (small gather kernel, one D2H)
+      TRY(s.big_list.reserve((size_t)n_over * 4));
+      TRY(s.big_S.reserve((size_t)n_over * 4));
+      TRY(s.big_A.reserve((size_t)n_over * 4));
+      TRY(s.h_plan.reserve((size_t)n_over * 8));
+      CU(cudaMemcpyAsync(s.big_list.p, order.data(), (size_t)n_over * 4, cudaMemcpyHostToDevice, s.stream));
+      k_gather_u32<<<(n_over + 255) / 256, 256, 0, s.stream>>>(s.rs_max_f.as<uint32_t>(), s.big_list.as<uint32_t>(), n_over, s.big_S.as<uint32_t>());
+      k_gather_u32<<<(n_over + 255) / 256, 256, 0, s.stream>>>(s.rs_sum_f.as<uint32_t>(), s.big_list.as<uint32_t>(), n_over, s.big_A.as<uint32_t>());
+      s.n_launches += 2;
+      CU(cudaMemcpyAsync(s.h_plan.p, s.big_S.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaMemcpyAsync(s.h_plan.as<uint32_t>() + n_over, s.big_A.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaStreamSynchronize(s.stream));
+      const uint32_t *mx = s.h_plan.as<uint32_t>(), *sm = mx + n_over;
+      const uint64_t limit_elems = (uint64_t)c->scratch_limit_bytes / 8;
+      uint32_t done = 0;
+      while (done < n_over && !arena_full) {
+        std::vector<uint32_t> list, bS, bA;
+        std::vector<uint64_t> boff;
+        uint64_t used = 0;
+        while (done < n_over) {
+          if (sm[done] == 0xFFFFFFFFu) return set_error(FEMGPU_ELIMIT, "read-strand %u: location lists too long", order[done]);
+          const uint64_t S = std::max<uint64_t>(64, 2ull * mx[done] + sm[done]);
+          const uint64_t Acap = std::max<uint64_t>(1, sm[done]);
+          if (S + Acap > limit_elems || S > 0xFFFFFFFFull)
+            return set_error(FEMGPU_ELIMIT, "read-strand %u needs %llu bytes of scratch (limit %lld)", order[done],
+                             (unsigned long long)((S + Acap) * 8), (long long)c->scratch_limit_bytes);
+          if (used + S + Acap > limit_elems && !list.empty()) break;
+          list.push_back(order[done]); boff.push_back(used); bS.push_back((uint32_t)S); bA.push_back((uint32_t)Acap);
+          used += S + Acap;
+          ++done;
+        }
+        const size_t nb = list.size();
+        TRY(s.scratch.reserve(used * 8));
+        TRY(s.big_list.reserve(nb * 4)); TRY(s.big_off.reserve(nb * 8)); TRY(s.big_S.reserve(nb * 4)); TRY(s.big_A.reserve(nb * 4));
+        CU(cudaMemcpyAsync(s.big_list.p, list.data(), nb * 4, cudaMemcpyHostToDevice, s.stream));
+        CU(cudaMemcpyAsync(s.big_off.p, boff.data(), nb * 8, cudaMemcpyHostToDevice, s.stream));
+        CU(cudaMemcpyAsync(s.big_S.p, bS.data(), nb * 4, cudaMemcpyHostToDevice, s.stream));
+        CU(cudaMemcpyAsync(s.big_A.p, bA.data(), nb * 4, cudaMemcpyHostToDevice, s.stream));
+        ca.big_list = s.big_list.as<uint32_t>(); ca.big_off = s.big_off.as<uint64_t>();
+        ca.big_S = s.big_S.as<uint32_t>(); ca.big_A = s.big_A.as<uint32_t>();
+        ca.scratch = s.scratch.as<uint64_t>();
+        ca.n_big = (uint32_t)nb;
+        k_cand_big<<<(unsigned)((nb + 3) / 4), 128, 0, s.stream>>>(ca);
+        ++s.n_launches;
+        CU(cudaGetLastError());
+        TRY(read_counters(s, &hc)); // also keeps the host vectors alive until the copies are done
+        if (hc.error_flag == 2) return set_error(FEMGPU_ECUDA, "internal: big-path scratch plan too small");
+        arena_full = hc.error_flag == 1;
+      }
+    }
+    if (!arena_full) break;
+    TRY(grow_arena(s));
+    CU(cudaMemsetAsync(&dc->cand_count, 0, sizeof(unsigned long long), s.stream));
+    CU(cudaMemsetAsync(&dc->overflow_count, 0, sizeof(uint32_t), s.stream));
+    CU(cudaMemsetAsync(&dc->error_flag, 0, sizeof(int), s.stream));
+  }
+  s.n_cand = hc.cand_count;
+  s.stats.num_candidates_before_filter = hc.total_before;
+  s.stats.num_candidates = hc.cand_count;
+  cudaEventRecord(s.ev[2], s.stream);
+  return 0;
+}
+
+// k_verify -> scan -> k_compact.  Records events 3 (after verify) and 4 (after compaction); leaves
+// s.n_maps and the device-side `maps` / `rs_map_first` arrays.
+static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
+  const uint64_t n_rs = 2ull * s.n_reads;
+  Counters *dc = s.counters.as<Counters>();
+  s.n_maps = 0;
+  if (s.n_reads == 0) {
+    cudaEventRecord(s.ev[3], s.stream);
+    cudaEventRecord(s.ev[4], s.stream);
+    return 0;
+  }
+  CU(cudaMemsetAsync(s.rs_map_count.p, 0, n_rs * 4, s.stream));
+  if (s.n_cand) {
+    VerifyArgs va;
+    va.ref.ref2 = c->ref2.as<uint32_t>();
+    va.ref.refn = c->ref_has_n ? c->refn.as<uint32_t>() : nullptr;
+    va.ref.rec_base = c->rec_base.as<uint64_t>();
+    va.ref.rec_len = c->rec_len.as<uint32_t>();
+    va.ref.n_rec = c->n_rec;
+    va.codes = s.codes.as<uint8_t>();
+    va.read_off = s.read_off.as<uint64_t>();
+    va.cand = s.cand.as<uint64_t>();
+    va.cand_rs = s.cand_rs.as<uint32_t>();
+    va.rs_cand_first = s.rs_cand_first.as<uint64_t>();
+    va.rs_cand_count = s.rs_cand_count.as<uint32_t>();
+    va.n_cand = s.n_cand;
+    va.e = pl.e;
+    va.result = s.result.as<uint32_t>();
+    va.rs_map_count = s.rs_map_count.as<uint32_t>();
+    const unsigned grid = (unsigned)((s.n_cand + 255) / 256);
+    if (c->ref_has_n) k_verify<true><<<grid, 256, 0, s.stream>>>(va);
+    else k_verify<false><<<grid, 256, 0, s.stream>>>(va);
+    ++s.n_launches;
+    CU(cudaGetLastError());
+  }
+  cudaEventRecord(s.ev[3], s.stream);
+  const unsigned n_blocks = (unsigned)((n_rs + SCAN_BLOCK - 1) / SCAN_BLOCK);
+  k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.rs_map_count.as<uint32_t>(), n_rs, s.block_sums.as<uint64_t>());
+  k_scan_blocks<<<1, 32, 0, s.stream>>>(s.block_sums.as<uint64_t>(), n_blocks, (uint64_t *)&dc->total_maps);
+  k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.rs_map_count.as<uint32_t>(), n_rs, s.block_sums.as<uint64_t>(),
+                                                     s.rs_map_first.as<uint64_t>(), (uint64_t *)&dc->total_maps);
+  s.n_launches += 3;
+  CU(cudaGetLastError());
+  Counters hc;
+  TRY(read_counters(s, &hc));
+  s.n_maps = hc.total_maps;
+  s.stats.num_mappings = hc.total_maps;
+  if (s.n_maps) {
+    TRY(s.maps.reserve(s.n_maps * 16));
+    CompactArgs pa;
+    pa.cand = s.cand.as<uint64_t>();
+    pa.result = s.result.as<uint32_t>();
+    pa.rs_cand_first = s.rs_cand_first.as<uint64_t>();
+    pa.rs_cand_count = s.rs_cand_count.as<uint32_t>();
+    pa.rs_map_first = s.rs_map_first.as<uint64_t>();
+    pa.rs_map_count = s.rs_map_count.as<uint32_t>();
+    pa.n_rs = (uint32_t)n_rs;
+    pa.maps = s.maps.as<ulonglong2>();
+    k_compact<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(pa);
+    ++s.n_launches;
+    CU(cudaGetLastError());
+  }
+  cudaEventRecord(s.ev[4], s.stream);
+  return 0;
+}

@@ -1,0 +1,161 @@
+/* femgpu.h -- C ABI of the B200 (sm_100a) implementation of the `FEM map` hot path.
+ *
+ * This is the drop-in boundary: plain C types only, one context per GPU.  A maintainer of the
+ * reference replaces the per-read calls inside the mapper thread (src/map.c:27-56) by one
+ * femgpu_map_batch() per SequenceBatch; INTEGRATION.md shows the exact C stub.  Every entry point
+ * names the reference interface it stands in for (file:line relative to the reference tree).
+ *
+ * Error convention: functions return 0 on success and a negative femgpu_status otherwise; the text
+ * is available from femgpu_last_error() (thread local).  Nothing here calls exit() or abort().
+ * There is no CPU fallback: without a CUDA device every call fails with FEMGPU_ENODEV.
+ */
+#ifndef FEMGPU_H_
+#define FEMGPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEMGPU_ABI_VERSION 1
+
+typedef enum {
+  FEMGPU_OK = 0,
+  FEMGPU_EINVAL = -1,   /* bad argument (e out of 0..7, a out of 0..2, k/step mismatch ...)   */
+  FEMGPU_ENODEV = -2,   /* no usable CUDA device                                               */
+  FEMGPU_ENOMEM = -3,   /* device or pinned-host allocation failed                             */
+  FEMGPU_ECUDA = -4,    /* a CUDA call or kernel failed                                        */
+  FEMGPU_ESTATE = -5,   /* index / reference not uploaded yet                                  */
+  FEMGPU_ELIMIT = -6    /* a read needs more scratch than the configured limit                 */
+} femgpu_status;
+
+typedef struct femgpu_ctx femgpu_ctx;
+
+/* src/FEM_map.c:63-72 (FEMArgs).  k/step <= 0: use the uploaded index header's values (the
+ * evidently intended behaviour); k=12, step=3 reproduces the unmodified reference binary, which
+ * never copies the header. */
+typedef struct {
+  int32_t k;    /* q-gram (window) size, 1..15   */
+  int32_t step; /* index step size               */
+  int32_t e;    /* error threshold 0..7          */
+  int32_t a;    /* additional q-grams 0..2       */
+} femgpu_params;
+
+/* src/utils.h:44-49 (Mapping).  16 bytes. */
+typedef struct {
+  uint64_t candidate_position;  /* (seq_index << 32) | band left edge                          */
+  int32_t end_position_offset;  /* mapping end = candidate_position + end_position_offset       */
+  uint8_t direction;            /* 0 forward, 1 reverse complement                              */
+  uint8_t edit_distance;
+  uint8_t reserved[2];
+} femgpu_mapping;
+
+/* One batch of reads: what a SequenceBatch (src/sequence_batch.h:15-24) holds, flattened.
+ * bases: the reads' sequence characters back to back (any case, non-ACGT = ambiguous);
+ * offsets[i]..offsets[i+1] delimit read i.  Host memory, pinned or pageable. */
+typedef struct {
+  const char *bases;
+  const uint64_t *offsets; /* n_reads + 1 entries */
+  uint32_t n_reads;
+} femgpu_batch;
+
+/* src/utils.h:55-61 (MappingStats) plus the count of reads the reference cannot process
+ * (undefined behaviour there, reported and skipped here -- SURVEY.md F2). */
+typedef struct {
+  uint64_t num_reads;
+  uint64_t num_mapped_reads;
+  uint64_t num_candidates_before_filter;
+  uint64_t num_candidates;
+  uint64_t num_mappings;
+  uint64_t num_infeasible_reads;
+} femgpu_stats;
+
+/* Result of one batch.  All pointers are owned by the context (pinned host memory) and stay valid
+ * until the next call that uses the same context slot.  mappings of read i are
+ * maps[first[i] .. first[i+1]) in the reference's emission order *before* process_mappings'
+ * sort (src/map.c:36,47: forward-strand hits in candidate order, then reverse-strand hits);
+ * femgpu_sort_mappings() applies src/align.c:57. */
+typedef struct {
+  const uint64_t *first;      /* n_reads + 1 */
+  const femgpu_mapping *maps; /* first[n_reads] records */
+  femgpu_stats stats;         /* this batch only */
+} femgpu_result;
+
+/* ---- life cycle ------------------------------------------------------------------------------ */
+int femgpu_abi_version(void);
+int femgpu_device_count(void);
+/* One context per GPU; owns its streams, device copies of index + reference, staging buffers. */
+femgpu_ctx *femgpu_create(int device);
+void femgpu_destroy(femgpu_ctx *ctx);
+const char *femgpu_last_error(void);
+
+/* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
+ * "acc_capacity", "l2_persist_lut".  Returns FEMGPU_EINVAL for unknown keys. */
+int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
+
+/* ---- resident data --------------------------------------------------------------------------- */
+/* Stands in for load_index (src/index.h:19, src/index.c:100-131): the arrays of the index file
+ * (`int k; int step; uint32 L[4^k+1]; size_t n; uint64 O[n]`, src/index.c:133-168) go to HBM
+ * verbatim.  Host pointers may be pageable. */
+int femgpu_upload_index(femgpu_ctx *ctx, int32_t k, int32_t step, const uint32_t *lookup_table,
+                        size_t lookup_table_size, const uint64_t *occurrence_table,
+                        size_t occurrence_table_size);
+/* Reads the index file itself (same layout) and uploads it in chunks without holding a second
+ * full host copy. */
+int femgpu_upload_index_file(femgpu_ctx *ctx, const char *index_path);
+/* Stands in for the reference SequenceBatch handed to every call (src/map.h:59): n records of
+ * raw characters; packed on the device to 2 bits per base plus an ambiguity mask. */
+int femgpu_upload_reference(femgpu_ctx *ctx, uint32_t n_records, const char *const *bases,
+                            const uint32_t *lengths);
+int femgpu_index_k(const femgpu_ctx *ctx);
+int femgpu_index_step(const femgpu_ctx *ctx);
+
+/* ---- the hot path ---------------------------------------------------------------------------- */
+/* Whole path for a batch = src/map.c:27-49 for every read: generate_group_seeding_candidates
+ * (src/filter.h:9) and verify_candidates (src/align.h:13) on both strands.  Synchronous:
+ * H2D of the batch, kernels, D2H of the compacted mappings all happen inside the call. */
+int femgpu_map_batch(femgpu_ctx *ctx, const femgpu_params *params, const femgpu_batch *batch,
+                     femgpu_result *result);
+
+/* Asynchronous form for double buffering (replaces the InputQueue/OutputQueue hand-off,
+ * src/input_queue.c:34-51, src/output_queue.c:46-58): `slot` is 0 or 1; submit returns once the
+ * batch has been staged, wait blocks until its result is in host memory. */
+int femgpu_submit_batch(femgpu_ctx *ctx, int slot, const femgpu_params *params,
+                        const femgpu_batch *batch);
+int femgpu_wait_batch(femgpu_ctx *ctx, int slot, femgpu_result *result);
+
+/* Stage-level entry points (tests, profiling, and callers that keep their own verification).
+ * Candidates: generate_group_seeding_candidates (src/filter.c:146-223) for both strands of every
+ * read.  Strand s of read i is "read-strand" 2*i+s; its candidates are
+ * cands[first[2i+s] .. first[2i+s+1]); before[2i+s] is its contribution to the "candidates before
+ * additional q-gram filter" counter; status[2i+s]: 0 ok, 1 reference returns 0 early
+ * (src/filter.c:168-172,180-182), 2 infeasible (reference UB).  Pointers: context-owned pinned
+ * memory, valid until the next call on the context. */
+typedef struct {
+  const uint64_t *first;   /* 2*n_reads + 1 */
+  const uint64_t *cands;
+  const uint32_t *before;  /* 2*n_reads */
+  const uint8_t *status;   /* 2*n_reads */
+} femgpu_candidates;
+int femgpu_candidates_batch(femgpu_ctx *ctx, const femgpu_params *params,
+                            const femgpu_batch *batch, femgpu_candidates *out);
+
+/* src/align.c:53-57 + src/ksort.h:98-151: the reference's per-read mapping order (host side,
+ * used by the SAM writer; exported so callers get the same permutation on ties). */
+void femgpu_sort_mappings(femgpu_mapping *maps, size_t n);
+
+/* ---- measurement hooks ------------------------------------------------------------------------ */
+/* Device time (CUDA events on the context's stream) of the kernels of the last finished batch, in
+ * milliseconds: [0] pack+seed, [1] candidates, [2] verify, [3] compaction, [4] whole device
+ * pipeline including H2D/D2H.  n_launches receives the number of kernel launches. */
+int femgpu_last_timings(femgpu_ctx *ctx, float ms[5], uint32_t *n_launches);
+/* Run the device pipeline of the last submitted batch again with inputs already resident in HBM
+ * (no H2D, no D2H of mappings); returns device milliseconds.  bench.py's `value`. */
+int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEMGPU_H_ */
