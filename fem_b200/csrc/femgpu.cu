@@ -211,6 +211,17 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   return 0;
 }
 
+extern "C" void *femgpu_alloc_pinned(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+    cudaGetLastError();
+    set_error(FEMGPU_ENOMEM, "cudaMallocHost of %zu bytes failed", bytes);
+    return nullptr;
+  }
+  return p;
+}
+extern "C" void femgpu_free_pinned(void *p) { if (p) cudaFreeHost(p); }
+
 extern "C" int femgpu_index_k(const femgpu_ctx *c) { return c ? c->idx_k : 0; }
 extern "C" int femgpu_index_step(const femgpu_ctx *c) { return c ? c->idx_step : 0; }
 

@@ -1,0 +1,253 @@
+/* fastx.c -- FASTA/FASTQ records into flattened batches (include/femhost.h).
+ *
+ * Record semantics are those of the reference's reader (klib kseq, src/kseq.h:185-226, driven by
+ * src/sequence_batch.c:44-121): header char '>' or '@', name = text up to the first white space,
+ * multi-line sequences, '+' line, quality lines until as long as the sequence, a trailing '\r' of
+ * a line is dropped, zero-length records are skipped, a short quality string is an error.
+ * The implementation is a block scanner (memchr over a 4 MiB window) writing straight into the
+ * batch's flat arrays.
+ */
+#include <ctype.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <zlib.h>
+
+#include "femhost.h"
+#include "host_internal.h"
+
+static __thread char g_err[512];
+const char *femhost_last_error(void) { return g_err; }
+int femhost_set_error(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+/* ---- records ----------------------------------------------------------------------------------- */
+void femhost_records_init(femhost_records *r, int pinned) {
+  memset(r, 0, sizeof *r);
+  r->pinned = pinned;
+}
+
+static void *grow(void *p, size_t old_bytes, size_t new_bytes, int pinned) {
+  if (!pinned) return realloc(p, new_bytes);
+  void *q = femgpu_alloc_pinned(new_bytes);
+  if (!q) return NULL;
+  if (p) { memcpy(q, p, old_bytes); femgpu_free_pinned(p); }
+  return q;
+}
+
+int femhost_records_reserve(femhost_records *r, size_t n_records, size_t n_bases, size_t n_names) {
+  if (n_records + 1 > r->cap_records) {
+    size_t m = r->cap_records ? r->cap_records : 1024;
+    while (m < n_records + 1) m *= 2;
+    uint64_t *bo = (uint64_t *)grow(r->base_off, r->cap_records * 8, m * 8, r->pinned);
+    uint64_t *no = (uint64_t *)realloc(r->name_off, m * 8);
+    uint8_t *hq = (uint8_t *)realloc(r->has_qual, m);
+    if (bo) r->base_off = bo;
+    if (no) r->name_off = no;
+    if (hq) r->has_qual = hq;
+    if (!bo || !no || !hq) return femhost_set_error(-3, "out of memory (%zu records)", m);
+    if (r->cap_records == 0) { r->base_off[0] = 0; r->name_off[0] = 0; }
+    r->cap_records = m;
+  }
+  if (n_bases > r->cap_bases) {
+    size_t m = r->cap_bases ? r->cap_bases : (1u << 16);
+    while (m < n_bases) m *= 2;
+    char *b = (char *)grow(r->bases, r->cap_bases, m, r->pinned);
+    char *q = (char *)realloc(r->quals, m);
+    if (b) r->bases = b;
+    if (q) r->quals = q;
+    if (!b || !q) return femhost_set_error(-3, "out of memory (%zu bases)", m);
+    r->cap_bases = m;
+  }
+  if (n_names > r->cap_names) {
+    size_t m = r->cap_names ? r->cap_names : (1u << 14);
+    while (m < n_names) m *= 2;
+    char *nm = (char *)realloc(r->names, m);
+    if (!nm) return femhost_set_error(-3, "out of memory (%zu name bytes)", m);
+    r->names = nm;
+    r->cap_names = m;
+  }
+  return 0;
+}
+
+void femhost_records_free(femhost_records *r) {
+  if (r->pinned) { femgpu_free_pinned(r->bases); femgpu_free_pinned(r->base_off); }
+  else { free(r->bases); free(r->base_off); }
+  free(r->quals); free(r->has_qual); free(r->names); free(r->name_off);
+  int pinned = r->pinned;
+  memset(r, 0, sizeof *r);
+  r->pinned = pinned;
+}
+
+/* ---- stream ------------------------------------------------------------------------------------- */
+#define FX_BUF (4 << 20)
+struct femhost_reader {
+  gzFile f;
+  unsigned char *buf;
+  int begin, end, is_eof, err;
+  int last_char;
+};
+
+femhost_reader *femhost_reader_open(const char *path) {
+  gzFile f = gzopen(path, "r");
+  if (!f) { femhost_set_error(-1, "Cannot find sequence file!"); return NULL; } /* src/sequence_batch.c:33 */
+  gzbuffer(f, 1 << 20);
+  femhost_reader *rd = (femhost_reader *)calloc(1, sizeof *rd);
+  rd->f = f;
+  rd->buf = (unsigned char *)malloc(FX_BUF);
+  return rd;
+}
+
+void femhost_reader_close(femhost_reader *rd) {
+  if (!rd) return;
+  gzclose(rd->f);
+  free(rd->buf);
+  free(rd);
+}
+
+/* refill; returns 0 when no more data */
+static inline int fx_fill(femhost_reader *rd) {
+  if (rd->is_eof) return 0;
+  rd->begin = 0;
+  rd->end = gzread(rd->f, rd->buf, FX_BUF);
+  if (rd->end <= 0) {
+    if (rd->end < 0) rd->err = 1;
+    rd->end = 0;
+    rd->is_eof = 1;
+    return 0;
+  }
+  return 1;
+}
+static inline int fx_getc(femhost_reader *rd) {
+  if (rd->begin >= rd->end && !fx_fill(rd)) return rd->err ? -3 : -1;
+  return rd->buf[rd->begin++];
+}
+
+/* Appends the rest of the current line to dst[*l ..] (dst = *pdst, grown through `reserve`);
+ * drops a trailing '\r' when the whole string is longer than one char (src/kseq.h:146).
+ * Returns -1 when nothing could be read because the stream is at its end. */
+typedef int (*fx_reserve_fn)(void *ctx, size_t need);
+static int fx_line(femhost_reader *rd, char **pdst, size_t base, size_t *l, fx_reserve_fn reserve, void *ctx) {
+  int got = 0;
+  for (;;) {
+    if (rd->begin >= rd->end && !fx_fill(rd)) break;
+    got = 1;
+    const unsigned char *p = rd->buf + rd->begin;
+    const int avail = rd->end - rd->begin;
+    const unsigned char *nl = (const unsigned char *)memchr(p, '\n', (size_t)avail);
+    const int n = nl ? (int)(nl - p) : avail;
+    if (reserve(ctx, base + *l + (size_t)n + 1)) return -3;
+    memcpy(*pdst + base + *l, p, (size_t)n);
+    *l += (size_t)n;
+    rd->begin += n + (nl ? 1 : 0);
+    if (nl) break;
+  }
+  if (!got) return rd->err ? -3 : -1;
+  if (*l > 1 && (*pdst)[base + *l - 1] == '\r') --*l;
+  return 0;
+}
+
+/* name: text up to the first white-space char; *delim receives that char (0 at end of stream) */
+static int fx_name(femhost_reader *rd, femhost_records *r, size_t base, size_t *l, int *delim) {
+  int got = 0;
+  *delim = 0;
+  *l = 0;
+  for (;;) {
+    if (rd->begin >= rd->end && !fx_fill(rd)) break;
+    got = 1;
+    int i = rd->begin;
+    while (i < rd->end && !isspace(rd->buf[i])) ++i;
+    const int n = i - rd->begin;
+    if (femhost_records_reserve(r, 0, 0, base + *l + (size_t)n + 1)) return -3;
+    memcpy(r->names + base + *l, rd->buf + rd->begin, (size_t)n);
+    *l += (size_t)n;
+    rd->begin = i + 1;
+    if (i < rd->end) { *delim = rd->buf[i]; break; }
+  }
+  if (!got) return rd->err ? -3 : -1;
+  r->names[base + *l] = 0;
+  return 0;
+}
+
+static int reserve_bases(void *ctx, size_t need) { return femhost_records_reserve((femhost_records *)ctx, 0, need, 0); }
+
+/* One record appended as record number r->n_records (not yet counted).  Returns its sequence
+ * length, -1 end of file, -2 truncated quality, -3 stream / memory error. */
+static long fx_record(femhost_reader *rd, femhost_records *r) {
+  int c;
+  if (rd->last_char == 0) { /* jump to the next header line */
+    while ((c = fx_getc(rd)) >= 0 && c != '>' && c != '@') {}
+    if (c < 0) return c;
+    rd->last_char = c;
+  }
+  const uint32_t i = r->n_records;
+  if (femhost_records_reserve(r, (size_t)i + 1, 0, 0)) return -3;
+  const size_t nb = r->name_off[i], sb = r->base_off[i];
+  size_t nl = 0, sl = 0, ql = 0;
+  int rc = fx_name(rd, r, nb, &nl, &c);
+  if (rc < 0) return rc;
+  if (c != '\n') { /* comment: read and dropped */
+    for (;;) {
+      if (rd->begin >= rd->end && !fx_fill(rd)) break;
+      const unsigned char *p = rd->buf + rd->begin;
+      const unsigned char *e = (const unsigned char *)memchr(p, '\n', (size_t)(rd->end - rd->begin));
+      if (e) { rd->begin += (int)(e - p) + 1; break; }
+      rd->begin = rd->end;
+    }
+  }
+  if (reserve_bases(r, sb + 2)) return -3;
+  while ((c = fx_getc(rd)) >= 0 && c != '>' && c != '+' && c != '@') {
+    if (c == '\n') continue;
+    if (reserve_bases(r, sb + sl + 2)) return -3;
+    r->bases[sb + sl++] = (char)c;
+    if (fx_line(rd, &r->bases, sb, &sl, reserve_bases, r) == -3) return -3;
+  }
+  if (c == '>' || c == '@') rd->last_char = c;
+  r->name_off[i + 1] = nb + nl + 1;
+  r->base_off[i + 1] = sb + sl;
+  r->has_qual[i] = 0;
+  if (c != '+') return c == -3 ? -3 : (long)sl; /* FASTA */
+  while ((c = fx_getc(rd)) >= 0 && c != '\n') {}
+  if (c == -1) return -2;
+  if (c == -3) return -3;
+  /* quality lines land in r->quals at the same offsets; the reserve keeps both arrays in step */
+  while ((rc = fx_line(rd, &r->quals, sb, &ql, reserve_bases, r)) >= 0 && ql < sl) {}
+  if (rc == -3) return -3;
+  rd->last_char = 0;
+  if (sl != ql) return -2;
+  r->has_qual[i] = ql != 0;
+  return (long)sl;
+}
+
+int64_t femhost_reader_next(femhost_reader *rd, uint32_t max_records, femhost_records *out) {
+  out->n_records = 0;
+  out->n_bases = 0;
+  if (femhost_records_reserve(out, 1, 16, 16)) return -3;
+  while (out->n_records < max_records) {
+    long l = fx_record(rd, out);
+    if (l == 0) continue; /* src/sequence_batch.c:50-52 */
+    if (l > 0) {
+      ++out->n_records;
+      out->n_bases += (uint64_t)l;
+    } else {
+      if (l != -1) /* src/sequence_batch.c:63-66 */
+        return femhost_set_error((int)l, "Didn't reach the end of sequence file, which might be corrupted!");
+      break;
+    }
+  }
+  return out->n_records;
+}
+
+int femhost_load_all(const char *path, femhost_records *out) {
+  femhost_reader *rd = femhost_reader_open(path);
+  if (!rd) return -1;
+  int64_t n = femhost_reader_next(rd, 0xFFFFFFF0u, out);
+  femhost_reader_close(rd);
+  return n < 0 ? (int)n : 0;
+}

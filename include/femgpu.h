@@ -91,6 +91,11 @@ femgpu_ctx *femgpu_create(int device);
 void femgpu_destroy(femgpu_ctx *ctx);
 const char *femgpu_last_error(void);
 
+/* Page-locked host memory for batch staging (replaces the kstring buffers a SequenceBatch owns,
+ * src/sequence_batch.h:15-24).  Returns NULL on failure. */
+void *femgpu_alloc_pinned(size_t bytes);
+void femgpu_free_pinned(void *p);
+
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
  * "acc_capacity", "l2_persist_lut".  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);

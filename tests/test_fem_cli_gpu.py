@@ -1,0 +1,115 @@
+"""GPU tests of the whole drop-in path: the `FEM` command line (fem_b200/bin/FEM -> libfemhost.so ->
+libfemgpu.so) must write the reference's SAM file byte for byte and print the same five counters.
+Checked against the golden fixtures (reference binaries' own output) and, on larger seeded inputs,
+against the oracle restatement (which tests/test_oracle_vs_ref.py pins to the reference)."""
+import glob
+import gzip
+import json
+import os
+import re
+import subprocess
+
+import pytest
+
+import oracle_lib as ol
+import synth
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+TAGS = sorted(os.path.basename(p)[:-5] for p in glob.glob(os.path.join(GOLD, "*.json")))
+
+
+def run_fem_map(fa, idx, fq, sam, e, a, threads=4, extra=()):
+    from fem_b200.host import FEM_BINARY
+    p = subprocess.run([FEM_BINARY, "map", "-e", str(e), "-a", str(a), "-t", str(threads), "--ref", fa, "--index", idx,
+                        "--read1", fq, "-o", sam, *extra], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert p.returncode == 0, p.stderr[-2000:]
+    vals = []
+    for tag in ("The number of read:", "The number of mapped read:", "The number of candidate before additional q-gram filter:",
+                "The number of candidate:", "The number of mapping:"):
+        m = re.search(re.escape(tag) + r" (\d+)", p.stderr)
+        assert m, p.stderr
+        vals.append(int(m.group(1)))
+    return tuple(vals)
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_cli_reproduces_golden_sam(tag, tmp_path):
+    from fem_b200.host import FEM_BINARY
+    with open(os.path.join(GOLD, tag + ".json")) as f:
+        meta = json.load(f)
+    fa, fq = (os.path.join(GOLD, "%s.%s" % (tag, s)) for s in ("ref.fa.gz", "reads.fq.gz"))
+    with gzip.open(os.path.join(GOLD, tag + ".sam.gz"), "rb") as f:
+        want = f.read()
+    idx, sam = str(tmp_path / "idx"), str(tmp_path / "out.sam")
+    subprocess.run([FEM_BINARY, "index", str(meta["k"]), str(meta["step"]), fa, idx], check=True, stderr=subprocess.DEVNULL)
+    extra = ("--asis",) if meta["binary"] == "asis" else ()
+    counters = run_fem_map(fa, idx, fq, sam, meta["e"], meta["a"], extra=extra)
+    c = meta["counters"]
+    assert counters == (c["num_reads"], c["num_mapped_reads"], c["num_candidates_before_filter"], c["num_candidates"],
+                        c["num_mappings"])
+    with open(sam, "rb") as f:
+        assert f.read() == want
+
+
+BIG = [
+    ("cli_cfg1", [600_000, 400_000, 300_000], 0.02, 30_000, 100, 3, 1, 12, 5),
+    ("cli_cfg2", [900_000, 500_000], 0.02, 20_000, 100, 5, 1, 12, 4),
+    ("cli_cfg3", [800_000, 400_000], 0.05, 10_000, 150, 7, 1, 12, 5),
+    ("cli_rep", [300_000, 200_000], 0.40, 4_000, 150, 7, 1, 12, 2),
+]
+
+
+@pytest.fixture(scope="module", params=BIG, ids=[c[0] for c in BIG])
+def big(request, tmp_path_factory):
+    from fem_b200.host import FEM_BINARY
+    tag, lens, rep, n_reads, l, e, a, k, step = request.param
+    d = tmp_path_factory.mktemp(tag)
+    records = synth.random_reference(sum(map(ord, tag)), lens, rep)
+    reads = synth.simulate_reads(sum(map(ord, tag)) + 1, records, n_reads, l, e)
+    fa, fq, idx = str(d / "ref.fa"), str(d / "reads.fq"), str(d / "idx")
+    synth.write_fasta(fa, records)
+    synth.write_fastq(fq, reads)
+    subprocess.run([FEM_BINARY, "index", str(k), str(step), fa, idx], check=True, stderr=subprocess.DEVNULL)
+    o = ol.Oracle(fasta=fa)
+    o.load_index(idx)
+    o.set_params(e, a)
+    want_sam = str(d / "oracle.sam")
+    st = o.map_file(fq, want_sam)
+    o.close()
+    with open(want_sam, "rb") as f:
+        want = f.read()
+    return dict(d=d, fa=fa, fq=fq, idx=idx, e=e, a=a, want=want, counters=st.as_tuple()[:5], n_reads=n_reads)
+
+
+def test_cli_matches_oracle_on_larger_inputs(big):
+    sam = str(big["d"] / "gpu.sam")
+    # small batches: many batches in flight on both slots, several SAM threads
+    counters = run_fem_map(big["fa"], big["idx"], big["fq"], sam, big["e"], big["a"], threads=8, extra=("--batch", "1500"))
+    assert counters == big["counters"]
+    with open(sam, "rb") as f:
+        assert f.read() == big["want"]
+    counters = run_fem_map(big["fa"], big["idx"], big["fq"], sam, big["e"], big["a"], threads=1)
+    assert counters == big["counters"]
+    with open(sam, "rb") as f:
+        assert f.read() == big["want"]
+
+
+def test_read_shards_concatenate_to_the_whole(big):
+    """One process per GPU: contiguous read shards, outputs concatenated in shard order (8e)."""
+    from fem_b200.host import HostMapper
+    m = HostMapper(big["fa"], big["idx"], 1)
+    n, parts, total = big["n_reads"], [], [0] * 5
+    cuts = [0, n // 3, n // 3 + 1, n]
+    for r in range(3):
+        out = str(big["d"] / ("shard%d.sam" % r))
+        st, _ = m.map_file(big["fq"], out, big["e"], big["a"], threads=4, batch_reads=997, skip_reads=cuts[r],
+                           max_reads=cuts[r + 1] - cuts[r], no_header=r > 0)
+        total = [x + y for x, y in zip(total, st[:5])]
+        with open(out, "rb") as f:
+            parts.append(f.read())
+    m.close()
+    assert b"".join(parts) == big["want"]
+    assert tuple(total) == big["counters"]

@@ -1,0 +1,196 @@
+"""CPU tests against the committed golden fixtures (tests/golden/, produced by the reference
+binaries -- see make_golden.py):
+  * the oracle restatement reproduces every golden SAM byte for byte, plus the counters and the
+    index file's sha256;
+  * the product's host side (fem_b200/host/*.c through libfemhost.so) does the same for the parts
+    that run on the host: FASTA/FASTQ parsing, `FEM index`, mapping order + traceback + SAM text
+    (fed with the oracle's mappings in emission order -- no GPU here);
+  * both shared libraries export every symbol their headers declare.
+"""
+import glob
+import gzip
+import hashlib
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLD = os.path.join(HERE, "golden")
+TAGS = sorted(os.path.basename(p)[:-5] for p in glob.glob(os.path.join(GOLD, "*.json")))
+
+
+def gold(tag):
+    with open(os.path.join(GOLD, tag + ".json")) as f:
+        meta = json.load(f)
+    fa, fq = (os.path.join(GOLD, "%s.%s" % (tag, s)) for s in ("ref.fa.gz", "reads.fq.gz"))
+    with gzip.open(os.path.join(GOLD, tag + ".sam.gz"), "rb") as f:
+        sam = f.read()
+    return meta, fa, fq, sam
+
+
+def oracle_for(meta, fa):
+    o = ol.Oracle(fasta=fa)
+    o.build_index(meta["k"], meta["step"])
+    if meta["binary"] == "asis":
+        o.set_params(meta["e"], meta["a"], 12, 3)
+    else:
+        o.set_params(meta["e"], meta["a"])
+    return o
+
+
+def parse_fastq_gz(path):
+    out = []
+    with gzip.open(path, "rb") as f:
+        lines = f.read().split(b"\n")
+    for i in range(0, len(lines) - 3, 4):
+        out.append((lines[i][1:].split()[0], lines[i + 1], lines[i + 3]))
+    return out
+
+
+def test_fixtures_present():
+    assert len(TAGS) >= 6
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_oracle_reproduces_golden(tag, tmp_path):
+    meta, fa, fq, sam = gold(tag)
+    o = oracle_for(meta, fa)
+    idx = str(tmp_path / "idx")
+    o.save_index(idx)
+    with open(idx, "rb") as f:
+        assert hashlib.sha256(f.read()).hexdigest() == meta["index_sha256"]
+    out = str(tmp_path / "o.sam")
+    st = o.map_file(fq, out)
+    c = meta["counters"]
+    assert st.as_tuple()[:5] == (c["num_reads"], c["num_mapped_reads"], c["num_candidates_before_filter"],
+                                 c["num_candidates"], c["num_mappings"])
+    with open(out, "rb") as f:
+        assert f.read() == sam
+    o.close()
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_host_index_matches_golden(tag, tmp_path):
+    from fem_b200 import host
+    meta, fa, _, _ = gold(tag)
+    ref = host.load_all(fa)
+    ix = host.Index.build(ref, meta["k"], meta["step"])
+    p = str(tmp_path / "idx")
+    ix.save(p)
+    with open(p, "rb") as f:
+        assert hashlib.sha256(f.read()).hexdigest() == meta["index_sha256"]
+    ix2 = host.Index.load(p)
+    k, step, lut, occ = ix.arrays()
+    k2, step2, lut2, occ2 = ix2.arrays()
+    assert (k, step) == (k2, step2) and np.array_equal(lut, lut2) and np.array_equal(occ, occ2)
+    # the command line writes the same file
+    p3 = str(tmp_path / "idx3")
+    subprocess.run([host.FEM_BINARY, "index", str(meta["k"]), str(meta["step"]), fa, p3], check=True,
+                   stderr=subprocess.DEVNULL)
+    with open(p3, "rb") as f:
+        assert hashlib.sha256(f.read()).hexdigest() == meta["index_sha256"]
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_host_reader_matches_python_parse(tag):
+    from fem_b200 import host
+    _, fa, fq, _ = gold(tag)
+    expect = parse_fastq_gz(fq)
+    got = [rec for batch in host.read_batches(fq, 64) for rec in batch]
+    assert got == expect
+    ref = host.load_all(fa)
+    with gzip.open(fa, "rb") as f:
+        chunks = f.read().split(b">")[1:]
+    assert len(ref) == len(chunks)
+    for i, ch in enumerate(chunks):
+        head, _, body = ch.partition(b"\n")
+        assert ref.name(i) == head.split()[0]
+        assert ref.seq(i) == body.replace(b"\n", b"")
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_host_sam_text_matches_golden(tag):
+    """mapping order (src/align.c:57), traceback, CIGAR/MD and SAM text of the product's host code."""
+    from fem_b200 import host
+    from fem_b200.api import MAPPING_DTYPE
+    meta, fa, fq, sam = gold(tag)
+    o = oracle_for(meta, fa)
+    ref = host.load_all(fa)
+    text = [host.sam_header(ref)]
+    most = 0
+    for name, seq, qual in parse_fastq_gz(fq):
+        emitted = []
+        for d, strand in enumerate((seq, ol.revcomp(seq))):
+            n, cands, _ = o.candidates(strand)
+            if n > 0:
+                emitted.extend(o.verify(strand, d, cands))
+        maps = np.zeros(len(emitted), dtype=MAPPING_DTYPE)
+        for j, (cand, end_off, direction, dist) in enumerate(emitted):
+            maps[j] = (cand, end_off, direction, dist, (0, 0))
+        most = max(most, len(emitted))
+        text.append(host.sam_read(ref, name, seq, qual, meta["e"], maps))
+    assert b"".join(text) == sam
+    if tag == "hdr_e7_s2_rep":
+        assert most > 64  # the in-place radix sort path of src/ksort.h:114-146 is exercised
+    o.close()
+
+
+def test_reader_edge_cases(tmp_path):
+    """multi-line FASTA, comments, CRLF, blank lines, empty records, FASTQ after FASTA headers."""
+    from fem_b200 import host
+    p = str(tmp_path / "x.fa")
+    with open(p, "wb") as f:
+        f.write(b"junk before\n>r1 comment here\nACGT\nAC\n\nGT\n>empty\n>r2\tc\r\nAAAA\r\nCC\r\n@q1 x\nACGTN\n+\nIIIII\n@q2\nAC\nGT\n+q2\nII\nII\n")
+    got = host.load_all(p).as_list()
+    assert got == [(b"r1", b"ACGTACGT", None), (b"r2", b"AAAACC", None), (b"q1", b"ACGTN", b"IIIII"), (b"q2", b"ACGT", b"IIII")]
+    bad = str(tmp_path / "bad.fq")
+    with open(bad, "wb") as f:
+        f.write(b"@q1\nACGT\n+\nII\n")
+    with pytest.raises(Exception):
+        host.load_all(bad)
+    with pytest.raises(Exception):
+        host.load_all(str(tmp_path / "missing.fa"))
+
+
+def _declared(header):
+    with open(os.path.join(ROOT, "include", header)) as f:
+        src = f.read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = set(re.findall(r"\b(fem(?:gpu|host)_[a-z0-9_]+)\s*\(", src))
+    inline = set(re.findall(r"static inline[^;{]*?\b(fem(?:gpu|host)_[a-z0-9_]+)\s*\(", src))
+    return sorted(names - inline)
+
+
+def test_libraries_export_every_declared_symbol():
+    import ctypes
+    from fem_b200.api import load_library
+    from fem_b200.host import load_host_library
+    dev, hst = load_library(), load_host_library()
+    gpu_syms, host_syms = _declared("femgpu.h"), _declared("femhost.h")
+    assert len(gpu_syms) >= 20 and len(host_syms) >= 18
+    for s in gpu_syms:
+        assert isinstance(getattr(dev, s), ctypes._CFuncPtr), s
+    for s in host_syms:
+        if s.startswith("femhost_"):
+            assert isinstance(getattr(hst, s), ctypes._CFuncPtr), s
+    assert dev.femgpu_abi_version() >= 1
+
+
+def test_no_fallback_without_a_device():
+    """Without a CUDA device the product must fail loudly, never compute on the host."""
+    from fem_b200.api import FemGpuError, Mapper, load_library
+    if load_library().femgpu_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(FemGpuError):
+        Mapper(0)
+    from fem_b200 import host
+    _, fa, _, _ = gold(TAGS[0])
+    with pytest.raises(FemGpuError):
+        host.HostMapper(fa, fa, 1)
