@@ -73,6 +73,10 @@ EXPORTS = {
     "femgpu_candidates_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Candidates)]),
     "femgpu_sort_mappings": (None, [C.c_void_p, C.c_size_t]),
     "femgpu_last_timings": (C.c_int, [C.c_void_p, C.POINTER(C.c_float * 5), C.POINTER(C.c_uint32)]),
+    "femgpu_alloc_pinned": (C.c_void_p, [C.c_size_t]),
+    "femgpu_free_pinned": (None, [C.c_void_p]),
+    "femgpu_measure_int32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double * 3)]),
+    "femgpu_last_work": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64 * 4)]),
     "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 4)]),
 }
 
@@ -231,6 +235,18 @@ class Mapper:
         n = C.c_uint32(0)
         _check(self.lib.femgpu_last_timings(self.h, C.byref(ms), C.byref(n)))
         return list(ms), n.value
+
+    def last_work(self):
+        """(verify columns executed, candidates, selected-seed occurrences, mappings) of the last batch"""
+        w = (C.c_uint64 * 4)()
+        _check(self.lib.femgpu_last_work(self.h, C.byref(w)))
+        return [int(x) for x in w]
+
+    def int32_peak(self):
+        """10^9 instr/s: (LOP3, IADD3, shift+logic)"""
+        g = (C.c_double * 3)()
+        _check(self.lib.femgpu_measure_int32_peak(self.h, C.byref(g)))
+        return list(g)
 
     def rerun_resident(self):
         tot = C.c_float(0)

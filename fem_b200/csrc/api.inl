@@ -170,6 +170,16 @@ extern "C" int femgpu_last_timings(femgpu_ctx *c, float ms[5], uint32_t *n_launc
   return 0;
 }
 
+extern "C" int femgpu_last_work(femgpu_ctx *c, uint64_t work[4]) {
+  if (!c || !work) return set_error(FEMGPU_EINVAL, "null argument");
+  const Slot &s = c->slot[c->last_slot];
+  work[0] = s.cols_executed;
+  work[1] = s.n_cand;
+  work[2] = s.stats.num_candidates_before_filter;
+  work[3] = s.n_maps;
+  return 0;
+}
+
 extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[4]) {
   if (!c) return set_error(FEMGPU_EINVAL, "null context");
   Slot &s = c->slot[c->last_slot];

@@ -15,6 +15,7 @@
 
 #include "common.cuh"
 #include "k_cand.cuh"
+#include "k_peak.cuh"
 #include "k_seed.cuh"
 #include "k_verify.cuh"
 
@@ -93,6 +94,7 @@ struct Counters {
   unsigned long long cand_count;
   unsigned long long total_before;
   unsigned long long total_maps;
+  unsigned long long cols_executed;
   uint32_t overflow_count;
   int error_flag;
 };
@@ -119,6 +121,7 @@ struct Slot {
   femgpu_stats stats{};
   float ms[5] = {0, 0, 0, 0, 0};
   uint32_t n_launches = 0;
+  uint64_t cols_executed = 0;
 };
 
 struct femgpu_ctx {
@@ -224,6 +227,38 @@ extern "C" void femgpu_free_pinned(void *p) { if (p) cudaFreeHost(p); }
 
 extern "C" int femgpu_index_k(const femgpu_ctx *c) { return c ? c->idx_k : 0; }
 extern "C" int femgpu_index_step(const femgpu_ctx *c) { return c ? c->idx_step : 0; }
+
+// INT32 pipe peak: instructions per second of the three kinds, 148 SMs x 8 CTAs x 256 threads
+extern "C" int femgpu_measure_int32_peak(femgpu_ctx *c, double giops[3]) {
+  if (!c || !giops) return set_error(FEMGPU_EINVAL, "null argument");
+  CU(cudaSetDevice(c->device));
+  uint32_t *d = nullptr;
+  CU(cudaMalloc(&d, 64));
+  cudaStream_t st = c->slot[0].stream;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int iters = 4096, blocks = c->sm_count * 8;
+  const double instr = (double)blocks * 256 * iters * 16 * 8;
+  for (int kind = 0; kind < 3; ++kind) {
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+      cudaEventRecord(e0, st);
+      if (kind == 0) k_int_peak<0><<<blocks, 256, 0, st>>>(d, iters, 12345u + rep);
+      else if (kind == 1) k_int_peak<1><<<blocks, 256, 0, st>>>(d, iters, 12345u + rep);
+      else k_int_peak<2><<<blocks, 256, 0, st>>>(d, iters, 12345u + rep);
+      cudaEventRecord(e1, st);
+      cudaEventSynchronize(e1);
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, e1);
+      if (rep && ms < best) best = ms;
+    }
+    giops[kind] = instr * (kind == 2 ? 2.0 : 1.0) / (best * 1e-3) / 1e9;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d);
+  CU(cudaGetLastError());
+  return 0;
+}
 
 #include "upload.inl"
 #include "pipeline.inl"

@@ -24,6 +24,7 @@ struct VerifyArgs {
   int e;
   uint32_t *result;            // out per candidate: dist<<16 | end_offset, or 0xFFFFFFFF
   uint32_t *rs_map_count;      // out per read-strand (atomic)
+  unsigned long long *cols_executed; // out: Myers columns actually computed (roofline accounting)
 };
 
 template <bool HAS_N>
@@ -40,7 +41,7 @@ __device__ __forceinline__ uint32_t ref_code_at(const DevRef &R, uint64_t g, uin
 template <bool HAS_N>
 __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
   const uint64_t ci = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (ci >= A.n_cand) return;
+  if (ci >= A.n_cand) return; // grid tail only: whole warps or the last partial one
   const uint32_t rs = A.cand_rs[ci];
   const uint32_t j = (uint32_t)(ci - A.rs_cand_first[rs]), n = A.rs_cand_count[rs];
   const uint32_t wmask = j < (n & ~7u) ? 0xFFFFu : 0xFFFFFFFFu; // align.c:12-13
@@ -62,7 +63,7 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
   }
   const uint32_t hi = 1u << (2 * e);
   uint32_t VP = 0, VN = 0;
-  int err = 0;
+  int err = 0, cols = l;
   bool dead = false;
   for (int i = 0; i < l; ++i, ++g) {               // align.c:117-134
     const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, e == 0 && i == 0);
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
     VN = X & HP;
     VP = HN | (~(X | HP) & wmask);
     err += 1 - (int)(D0 & 1u);
-    if (err > 3 * e) { dead = true; break; }
+    if (err > 3 * e) { dead = true; cols = i + 1; break; }
     p0 >>= 1; p1 >>= 1; p2 >>= 1; p3 >>= 1; p4 >>= 1;
   }
   uint32_t out = 0xFFFFFFFFu;
@@ -94,6 +95,9 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
     }
   }
   A.result[ci] = out;
+  const uint32_t live = __activemask();
+  const uint32_t warp_cols = __reduce_add_sync(live, (uint32_t)cols);
+  if (lane_id() == (uint32_t)(__ffs(live) - 1)) atomicAdd(A.cols_executed, (unsigned long long)warp_cols);
 }
 
 // ---- exclusive scan of uint32 counts into uint64 offsets (3 small kernels) ----------------------

@@ -252,6 +252,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     va.e = pl.e;
     va.result = s.result.as<uint32_t>();
     va.rs_map_count = s.rs_map_count.as<uint32_t>();
+    va.cols_executed = &dc->cols_executed;
     const unsigned grid = (unsigned)((s.n_cand + 255) / 256);
     if (c->ref_has_n) k_verify<true><<<grid, 256, 0, s.stream>>>(va);
     else k_verify<false><<<grid, 256, 0, s.stream>>>(va);
@@ -269,6 +270,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
   Counters hc;
   TRY(read_counters(s, &hc));
   s.n_maps = hc.total_maps;
+  s.cols_executed = hc.cols_executed;
   s.stats.num_mappings = hc.total_maps;
   if (s.n_maps) {
     TRY(s.maps.reserve(s.n_maps * 16));

@@ -121,6 +121,11 @@ class Records:
     def name(self, i):
         return C.string_at(self.c.names + self.c.name_off[i])
 
+    def as_batch(self):
+        """femgpu_batch view of these records (no copy; valid while the records live)."""
+        from .api import Batch
+        return Batch(self.c.bases, C.cast(self.c.base_off, C.c_void_p), self.c.n_records)
+
     def as_list(self):
         return [(self.name(i), self.seq(i), self.qual(i)) for i in range(len(self))]
 

@@ -156,9 +156,19 @@ void femgpu_sort_mappings(femgpu_mapping *maps, size_t n);
  * milliseconds: [0] pack+seed, [1] candidates, [2] verify, [3] compaction, [4] whole device
  * pipeline including H2D/D2H.  n_launches receives the number of kernel launches. */
 int femgpu_last_timings(femgpu_ctx *ctx, float ms[5], uint32_t *n_launches);
+/* Work counters of the last finished batch, the numerators of the roofline figures: [0] banded
+ * Myers columns actually computed by the verification kernel, [1] candidates verified,
+ * [2] occurrence-table entries of the selected seeds ("candidates before additional q-gram
+ * filter", src/filter.c:202), [3] mappings emitted. */
+int femgpu_last_work(femgpu_ctx *ctx, uint64_t work[4]);
 /* Run the device pipeline of the last submitted batch again with inputs already resident in HBM
  * (no H2D, no D2H of mappings); returns device milliseconds.  bench.py's `value`. */
 int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[4]);
+
+/* INT32 pipe peak of the device in 10^9 instructions per second, measured with dependency-chain
+ * free kernels: [0] LOP3 (logic), [1] IADD3 (add), [2] shift+logic pairs as in the Myers column.
+ * The denominator of the verification kernel's roofline. */
+int femgpu_measure_int32_peak(femgpu_ctx *ctx, double giops[3]);
 
 #ifdef __cplusplus
 }
