@@ -22,7 +22,7 @@ static int stage_batch(femgpu_ctx *c, Slot &s, const femgpu_params *p, const fem
   int l_max = 0;
   TRY(scan_batch(b, &n_bases, &l_max));
   TRY(make_plan(c, p, l_max, pl));
-  if (pl->seed_smem > c->smem_optin || pl->cand_smem > c->smem_optin)
+  if (pl->seed_smem > c->smem_optin || pl->cand_smem > c->smem_optin || pl->hash_smem > c->smem_optin)
     return set_error(FEMGPU_EINVAL, "shared-memory plan too large (seed %zu, cand %zu bytes)", pl->seed_smem, pl->cand_smem);
   TRY(slot_reserve(c, s, *pl, b->n_reads, n_bases));
   s.params = *p;

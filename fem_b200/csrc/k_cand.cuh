@@ -38,6 +38,9 @@ struct CandArgs {
   int *error_flag;                 // 1: arena full
   // fast-path shared-memory plan (elements per warp)
   uint32_t S, Acap;
+  // list mode of k_cand: the read-strands the hash path (k_cand_hash) handed on
+  const uint32_t *rs_list;
+  uint32_t n_list;
   // big path
   const uint32_t *big_list;        // read-strand ids
   const uint64_t *big_off;         // scratch offset (elements) per entry
@@ -236,8 +239,11 @@ __device__ void rs_emit_candidates(const CandArgs &A, uint64_t rs, uint32_t lane
 __global__ void __launch_bounds__(128) k_cand(CandArgs A) {
   extern __shared__ uint64_t smem_cand[];
   const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
-  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-  if (rs >= A.n_rs) return;
+  uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+  if (A.rs_list) {
+    if (rs >= A.n_list) return;
+    rs = A.rs_list[rs];
+  } else if (rs >= A.n_rs) return;
   if (A.rs_status[rs] != RS_OK) {
     if (lane == 0) { A.rs_cand_first[rs] = 0; A.rs_cand_count[rs] = 0; }
     return;

@@ -2,9 +2,11 @@
 
 struct Plan { // derived from params + the batch
   int k, step, e, a, Q, s;
-  int l_max, n_words_max, ns_max, w_max;
+  int l_max, n_words_max, ns_max, w_max, lane_dp;
   size_t seed_smem;   // bytes per block of k_seed
   size_t cand_smem;   // bytes per block of k_cand
+  uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
+  size_t hash_smem;
 };
 
 static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
@@ -26,9 +28,22 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   pl->l_max = std::max(l_max, 1);
   pl->n_words_max = (pl->l_max + 15) / 16 + 1;
   pl->ns_max = std::max(pl->l_max - pl->k + 1, 1);
-  pl->w_max = pl->ns_max / pl->step + 1;
-  pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q) * 4; // 4 warps
+  // widest DP table of the batch: W = n_g - Q*s + 1 columns for the longest read's group 0
+  pl->w_max = std::max(pl->ns_max / pl->step - pl->Q * pl->s + 1, 1);
+  // one lane per group pays Q*W serial steps, the warp scan pays step*Q*ceil(W/32) rounds of ~7x the cost
+  pl->lane_dp = c->seed_dp_mode == 1 ? 1 : c->seed_dp_mode == 2 ? 0 : pl->w_max <= 8 * pl->step;
+  pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4; // 4 warps
   pl->cand_smem = (size_t)4 * (c->sort_capacity + c->acc_capacity) * 8;
+  // hash path: room for 4x the expected location-list total of a group on a uniform index
+  uint32_t T = c->hash_slots;
+  if (!T) {
+    const double mean = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q;
+    T = pow2_ceil_u32((uint32_t)std::min(1024.0, std::max(128.0, 4.0 * mean)));
+  }
+  pl->hash_T = T;
+  pl->hash_shift = 64;
+  for (uint32_t t = T; t > 1; t >>= 1) --pl->hash_shift;
+  pl->hash_smem = 4 * cand_hash_smem_bytes_per_warp(T);
   return 0;
 }
 
@@ -107,6 +122,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.inf = (uint32_t)c->n_occ;
   sa.k = pl.k; sa.step = pl.step; sa.e = pl.e; sa.a = pl.a; sa.Q = pl.Q; sa.s = pl.s;
   sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
+  sa.lane_dp = pl.lane_dp;
   sa.codes = s.codes.as<uint8_t>();
   sa.rs_status = s.rs_status.as<uint8_t>();
   sa.rs_before = s.rs_before.as<uint32_t>();
@@ -139,6 +155,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.error_flag = &dc->error_flag;
   ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
+  if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
 
   Counters hc;
   for (int attempt = 0;; ++attempt) {
@@ -146,11 +163,28 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand = s.cand.as<uint64_t>();
     ca.cand_rs = s.cand_rs.as<uint32_t>();
     ca.cand_cap = s.cand_cap;
-    k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
+    ca.rs_list = nullptr;
+    ca.n_list = 0;
+    if (c->cand_mode == 0) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
+    else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
     ++s.n_launches;
     CU(cudaGetLastError());
     TRY(read_counters(s, &hc));
     bool arena_full = hc.error_flag == 1;
+    if (c->cand_mode == 0 && !arena_full && hc.overflow_count) {
+      // ---- sort path for the read-strands the hash path handed on ----------------------------------
+      const uint32_t n1 = hc.overflow_count;
+      TRY(s.hash_list.reserve((size_t)n1 * 4));
+      CU(cudaMemcpyAsync(s.hash_list.p, s.overflow_list.p, (size_t)n1 * 4, cudaMemcpyDeviceToDevice, s.stream));
+      CU(cudaMemsetAsync(&dc->overflow_count, 0, sizeof(uint32_t), s.stream));
+      ca.rs_list = s.hash_list.as<uint32_t>();
+      ca.n_list = n1;
+      k_cand<<<(n1 + 3) / 4, 128, pl.cand_smem, s.stream>>>(ca);
+      ++s.n_launches;
+      CU(cudaGetLastError());
+      TRY(read_counters(s, &hc));
+      arena_full = hc.error_flag == 1;
+    }
     if (!arena_full && hc.overflow_count) {
       // ---- big path: plan scratch slices on the host, run in rounds within the scratch limit ----
       const uint32_t n_over = hc.overflow_count;

@@ -69,11 +69,17 @@ static void fifo_close(fifo *q) {
 
 /* ---- mapper: resident data ---------------------------------------------------------------------- */
 #define FEM_MAX_GPUS 16
+struct batch;
 struct femhost_mapper {
   femhost_records ref;
   int n_gpus;
   femgpu_ctx *ctx[FEM_MAX_GPUS];
+  /* batch objects (pinned staging, result copies, SAM text buffers) live as long as the mapper,
+   * so a second run pays for none of their allocations */
+  struct batch *pool;
+  size_t n_pool;
 };
+static void pool_free(femhost_mapper *m);
 
 femhost_mapper *femhost_mapper_create(const char *ref_path, const char *index_path, int n_gpus, const int *gpu_ids) {
   if (!ref_path || !index_path || n_gpus < 1 || n_gpus > FEM_MAX_GPUS) {
@@ -115,6 +121,7 @@ fail:
 
 void femhost_mapper_destroy(femhost_mapper *m) {
   if (!m) return;
+  pool_free(m);
   for (int g = 0; g < m->n_gpus; ++g) femgpu_destroy(m->ctx[g]);
   femhost_records_free(&m->ref);
   free(m);
@@ -143,6 +150,21 @@ struct batch {
   size_t cap_chunks;
   int chunks_left;          /* guarded by run->mu */
 };
+
+static void pool_free(femhost_mapper *m) {
+  for (size_t i = 0; i < m->n_pool; ++i) {
+    batch *b = &m->pool[i];
+    femhost_records_free(&b->reads);
+    free(b->first);
+    free(b->maps);
+    for (size_t c = 0; c < b->cap_chunks; ++c) femhost_str_free(&b->text[c]);
+    free(b->text);
+    free(b->items);
+  }
+  free(m->pool);
+  m->pool = NULL;
+  m->n_pool = 0;
+}
 
 typedef struct {
   femhost_mapper *m;
@@ -365,17 +387,20 @@ int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const ch
   const double t_start = femhost_now();
   const int n_gpu_threads = 2 * m->n_gpus, n_workers = opt->n_threads;
   r.n_batches = (size_t)(2 * n_gpu_threads + 2);
-  batch *pool = (batch *)calloc(r.n_batches, sizeof(batch));
+  if (m->n_pool != r.n_batches) {
+    pool_free(m);
+    m->pool = (batch *)calloc(r.n_batches, sizeof(batch));
+    m->n_pool = r.n_batches;
+    for (size_t i = 0; i < r.n_batches; ++i) femhost_records_init(&m->pool[i].reads, 1);
+  }
+  batch *pool = m->pool;
   r.done = (batch **)calloc(r.n_batches, sizeof(batch *));
   fifo_init(&r.q_free, r.n_batches + 1);
   fifo_init(&r.q_parsed, r.n_batches + 1);
   fifo_init(&r.q_work, 1 << 16);
   pthread_mutex_init(&r.mu, NULL);
   pthread_cond_init(&r.batch_done, NULL);
-  for (size_t i = 0; i < r.n_batches; ++i) {
-    femhost_records_init(&pool[i].reads, 1);
-    fifo_push(&r.q_free, &pool[i]);
-  }
+  for (size_t i = 0; i < r.n_batches; ++i) fifo_push(&r.q_free, &pool[i]);
   if (!opt->no_header) { /* src/output_queue.c:93-116 */
     femhost_str hdr = {0, 0, 0};
     if (femhost_sam_header(&m->ref, &hdr) == 0) {
@@ -405,15 +430,7 @@ int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const ch
   if (r.out && fclose(r.out) != 0) run_fail(&r, "closing the SAM file failed");
   r.tm.wall = femhost_now() - t_start;
   femhost_reader_close(r.rd);
-  for (size_t i = 0; i < r.n_batches; ++i) {
-    femhost_records_free(&pool[i].reads);
-    free(pool[i].first);
-    free(pool[i].maps);
-    for (size_t c = 0; c < pool[i].cap_chunks; ++c) femhost_str_free(&pool[i].text[c]);
-    free(pool[i].text);
-    free(pool[i].items);
-  }
-  free(pool); free(r.done); free(th_worker); free(wa);
+  free(r.done); free(th_worker); free(wa);
   fifo_destroy(&r.q_free); fifo_destroy(&r.q_parsed); fifo_destroy(&r.q_work);
   pthread_mutex_destroy(&r.mu);
   pthread_cond_destroy(&r.batch_done);

@@ -179,8 +179,49 @@ static int reserve_bases(void *ctx, size_t need) { return femhost_records_reserv
 
 /* One record appended as record number r->n_records (not yet counted).  Returns its sequence
  * length, -1 end of file, -2 truncated quality, -3 stream / memory error. */
+/* Fast path for the common shape: a four-line FASTQ record that lies completely inside the
+ * buffer -- "@name[ comment]\n" "SEQ\n" "+...\n" "QUAL\n" with |QUAL| == |SEQ| > 0 and no '\r'.
+ * For such a record the general scanner below produces exactly these fields, so it is parsed with
+ * four memchr calls.  Returns the sequence length, or -4 when the record is not of that shape
+ * (nothing consumed; the general scanner takes over). */
+static long fx_record_fast(femhost_reader *rd, femhost_records *r) {
+  const unsigned char *p = rd->buf + rd->begin, *end = rd->buf + rd->end;
+  if (p >= end || *p != '@') return -4;
+  const unsigned char *e1 = (const unsigned char *)memchr(p, '\n', (size_t)(end - p));
+  if (!e1 || e1 + 1 >= end) return -4;
+  const unsigned char *s = e1 + 1;
+  if (*s == '\n' || *s == '>' || *s == '@' || *s == '+') return -4;
+  const unsigned char *e2 = (const unsigned char *)memchr(s, '\n', (size_t)(end - s));
+  if (!e2 || e2 + 1 >= end || e2[1] != '+' || e2[-1] == '\r') return -4;
+  const unsigned char *e3 = (const unsigned char *)memchr(e2 + 1, '\n', (size_t)(end - e2 - 1));
+  if (!e3) return -4;
+  const size_t sl = (size_t)(e2 - s);
+  const unsigned char *q = e3 + 1;
+  if ((size_t)(end - q) < sl + 1 || q[sl] != '\n' || q[sl - 1] == '\r') return -4;
+  if (memchr(q, '\n', sl)) return -4; /* a shorter first quality line: general path */
+  const unsigned char *n0 = p + 1, *n1 = n0;
+  while (n1 < e1 && !isspace(*n1)) ++n1;
+  const size_t nl = (size_t)(n1 - n0);
+  const uint32_t i = r->n_records;
+  const size_t nb = r->name_off[i], sb = r->base_off[i];
+  if (femhost_records_reserve(r, (size_t)i + 2, sb + sl + 2, nb + nl + 2)) return -3;
+  memcpy(r->names + nb, n0, nl);
+  r->names[nb + nl] = 0;
+  memcpy(r->bases + sb, s, sl);
+  memcpy(r->quals + sb, q, sl);
+  r->name_off[i + 1] = nb + nl + 1;
+  r->base_off[i + 1] = sb + sl;
+  r->has_qual[i] = 1;
+  rd->begin = (int)(q + sl + 1 - rd->buf);
+  return (long)sl;
+}
+
 static long fx_record(femhost_reader *rd, femhost_records *r) {
   int c;
+  if (rd->last_char == 0) {
+    const long fast = fx_record_fast(rd, r);
+    if (fast != -4) return fast;
+  }
   if (rd->last_char == 0) { /* jump to the next header line */
     while ((c = fx_getc(rd)) >= 0 && c != '>' && c != '@') {}
     if (c < 0) return c;

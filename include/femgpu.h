@@ -97,7 +97,8 @@ void *femgpu_alloc_pinned(size_t bytes);
 void femgpu_free_pinned(void *p);
 
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
- * "acc_capacity", "l2_persist_lut".  Returns FEMGPU_EINVAL for unknown keys. */
+ * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan),
+ * "cand_mode" (0 hash path first, 1 sort path only), "hash_slots" (0 automatic).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 
 /* ---- resident data --------------------------------------------------------------------------- */

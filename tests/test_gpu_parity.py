@@ -88,10 +88,34 @@ def test_candidates_big_path(setup):
     setup.mapper.set_option("sort_capacity", 32)
     setup.mapper.set_option("acc_capacity", 2)
     try:
-        check_candidates(setup, seqs)
+        for mode in (1, 0):  # sort path for everything / hash path first
+            setup.mapper.set_option("cand_mode", mode)
+            check_candidates(setup, seqs)
     finally:
+        setup.mapper.set_option("cand_mode", 0)
         setup.mapper.set_option("sort_capacity", 1024)
         setup.mapper.set_option("acc_capacity", 256)
+
+
+@pytest.mark.parametrize("slots", [32, 64, 4096])
+def test_candidates_hash_path_table_sizes(setup, slots):
+    """k_cand_hash with tables from far too small (most read-strands handed on to the sort path)
+    to generous; and the sort path alone must agree with it."""
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("hash_slots", slots)
+    try:
+        check_candidates(setup, seqs)
+    finally:
+        setup.mapper.set_option("hash_slots", 0)
+
+
+def test_candidates_sort_path_only(setup):
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("cand_mode", 1)
+    try:
+        check_candidates(setup, seqs)
+    finally:
+        setup.mapper.set_option("cand_mode", 0)
 
 
 def test_small_arena_retries(setup):
@@ -140,3 +164,14 @@ def test_double_buffered_submit_matches_sync(setup):
     assert np.array_equal(np.concatenate([m0, m1]), m_all)
     assert np.array_equal(np.concatenate([f0, f1[1:] + f0[-1]]), f_all)
     assert tuple(a + b for a, b in zip(st0, st1)) == st_all
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_seed_selection_forms_agree(setup, mode):
+    """k_seed's two DP forms (one lane per group / warp scan) must select the same seeds."""
+    seqs = [r[1] for r in setup.reads[:400]]
+    setup.mapper.set_option("seed_dp_mode", mode)
+    try:
+        check_candidates(setup, seqs)
+    finally:
+        setup.mapper.set_option("seed_dp_mode", 0)
