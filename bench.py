@@ -10,7 +10,7 @@ its own 1 M reads against the replicated index; there is no collective on the da
 A "step" is one pass of the hot path over the rank's reads.
 
   value  reads/s with the reads already resident in HBM (femgpu_rerun_resident: seed ->
-         candidates -> verify -> compaction), CUDA-event time summed over the K steps, max over ranks
+         candidates -> verify -> compaction -> traceback), CUDA-event time summed over the K steps, max over ranks
   e2e    reads/s of the whole `FEM map` run through the C ABI (femhost_map_file): FASTQ parse from
          the page cache, pinned H2D, kernels, D2H, mapping order + traceback + SAM text, file written
          to tmpfs -- the same window as the reference's own "Time:" line (src/FEM_map.c:172-219)
@@ -257,15 +257,15 @@ def run_ours(args):
     # ---- resident leg: `value` -----------------------------------------------------------------
     _check(lib.femgpu_map_batch(ctx, C.byref(params), C.byref(batch), C.byref(res)))  # stages the reads in HBM
     stats = res.stats.as_tuple()
-    tot, st = C.c_float(0), (C.c_float * 4)()
+    tot, st = C.c_float(0), (C.c_float * 5)()
     for _ in range(max(args.warmup, 3)):
         _check(lib.femgpu_rerun_resident(ctx, C.byref(tot), C.byref(st)))
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     wall0 = time.perf_counter()
-    dev_ms, stage_ms, launches = 0.0, [0.0] * 4, 0
-    ms5, nl = (C.c_float * 5)(), C.c_uint32(0)
+    dev_ms, stage_ms, launches = 0.0, [0.0] * 5, 0
+    ms5, nl = (C.c_float * 6)(), C.c_uint32(0)
     for _ in range(args.steps):
         _check(lib.femgpu_rerun_resident(ctx, C.byref(tot), C.byref(st)))
         dev_ms += tot.value
@@ -301,17 +301,18 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel -----------------------------------------------------------
     hbm_peak, peak_src = load_peaks()
-    per = [m / args.steps for m in stage_ms]  # ms per step: seed, candidates, verify, compaction
+    per = [m / args.steps for m in stage_ms]  # ms per step: seed, candidates, verify, compaction, traceback
     n_s = w["read_len"] - w["k"] + 1
     cols, n_cand, c_before, n_maps = [int(x) for x in work]
     algo = {"k_seed": 16.0 * n_s * n_reads + w["read_len"] * n_reads,          # two LUT words per q-gram and strand + the read
             "k_cand": 8.0 * c_before,                                           # occurrence words of the selected seeds
             "k_verify": n_cand * ((w["read_len"] + 2 * w["e"] + 3) // 4) + 16.0 * n_maps,  # 2-bit window per candidate
-            "k_compact": 16.0 * n_maps + 4.0 * n_cand}
-    names = ["k_seed", "k_cand", "k_verify", "k_compact"]
+            "k_compact": 16.0 * n_maps + 4.0 * n_cand,
+            "k_trace": n_maps * (2.0 * ((w["read_len"] + 2 * w["e"] + 3) // 4) + w["read_len"] + 40.0)}  # window twice, read, 40-byte record
+    names = ["k_seed", "k_cand", "k_verify", "k_compact", "k_trace"]
     kernels = {n: {"ms": per[i], "algorithmic_bytes": algo[n], "gbs": algo[n] / (per[i] * 1e-3) / 1e9 if per[i] > 0 else None}
                for i, n in enumerate(names)}
-    top = max(range(4), key=lambda i: per[i])
+    top = max(range(5), key=lambda i: per[i])
     ach = kernels[names[top]]["gbs"]
     roofline = {"kernel": names[top], "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                 "traffic": None, "peak_source": peak_src, "share_of_step": per[top] / sum(per)}

@@ -46,8 +46,18 @@ class Stats(C.Structure):
         return tuple(int(getattr(self, n)) for n, _ in self._fields_)
 
 
+class AlignmentRec(C.Structure):
+    _fields_ = [("start", C.c_int16), ("n_cigar", C.c_uint8), ("reserved", C.c_uint8), ("cigar", C.c_uint16 * 18)]
+
+
+ALIGNMENT_DTYPE = np.dtype([("start", "<i2"), ("n_cigar", "u1"), ("reserved", "u1"), ("cigar", "<u2", (18,))])
+assert ALIGNMENT_DTYPE.itemsize == 40 == C.sizeof(AlignmentRec)
+ALN_HOST = 0xFF
+
+
 class Result(C.Structure):
-    _fields_ = [("first", C.POINTER(C.c_uint64)), ("maps", C.POINTER(MappingRec)), ("stats", Stats)]
+    _fields_ = [("first", C.POINTER(C.c_uint64)), ("maps", C.POINTER(MappingRec)), ("stats", Stats),
+                ("alns", C.POINTER(AlignmentRec))]
 
 
 class Candidates(C.Structure):
@@ -72,12 +82,13 @@ EXPORTS = {
     "femgpu_wait_batch": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Result)]),
     "femgpu_candidates_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Candidates)]),
     "femgpu_sort_mappings": (None, [C.c_void_p, C.c_size_t]),
-    "femgpu_last_timings": (C.c_int, [C.c_void_p, C.POINTER(C.c_float * 5), C.POINTER(C.c_uint32)]),
+    "femgpu_sort_mappings_aln": (None, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "femgpu_last_timings": (C.c_int, [C.c_void_p, C.POINTER(C.c_float * 6), C.POINTER(C.c_uint32)]),
     "femgpu_alloc_pinned": (C.c_void_p, [C.c_size_t]),
     "femgpu_free_pinned": (None, [C.c_void_p]),
     "femgpu_measure_int32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double * 3)]),
     "femgpu_last_work": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64 * 4)]),
-    "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 4)]),
+    "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 5)]),
 }
 
 _lib = None
@@ -102,6 +113,14 @@ def load_library():
 def _check(rc):
     if rc != 0:
         raise FemGpuError("femgpu error %d: %s" % (rc, load_library().femgpu_last_error().decode(errors="replace")))
+
+
+def sort_mappings_aln(maps: np.ndarray, alns: np.ndarray):
+    """In-place reference order of one read's mappings with their device alignments carried along."""
+    assert maps.dtype == MAPPING_DTYPE and alns.dtype == ALIGNMENT_DTYPE and maps.shape == alns.shape
+    assert maps.flags.c_contiguous and alns.flags.c_contiguous
+    load_library().femgpu_sort_mappings_aln(maps.ctypes.data, alns.ctypes.data, maps.shape[0])
+    return maps, alns
 
 
 def sort_mappings(maps: np.ndarray):
@@ -190,6 +209,9 @@ class Mapper:
             maps = np.frombuffer(C.string_at(res.maps, n * 16), dtype=MAPPING_DTYPE).copy()
         else:
             maps = np.zeros(0, dtype=MAPPING_DTYPE)
+        # device start/CIGAR per mapping (k_trace), parallel to maps; None when switched off
+        self.last_alignments = (np.frombuffer(C.string_at(res.alns, n * 40), dtype=ALIGNMENT_DTYPE).copy()
+                                if n and res.alns else None)
         return first, maps, res.stats.as_tuple()
 
     def map_batch(self, reads, e, a=1, k=0, step=0):
@@ -231,7 +253,7 @@ class Mapper:
         return first, cands, before, status
 
     def last_timings(self):
-        ms = (C.c_float * 5)()
+        ms = (C.c_float * 6)()
         n = C.c_uint32(0)
         _check(self.lib.femgpu_last_timings(self.h, C.byref(ms), C.byref(n)))
         return list(ms), n.value
@@ -250,6 +272,6 @@ class Mapper:
 
     def rerun_resident(self):
         tot = C.c_float(0)
-        st = (C.c_float * 4)()
+        st = (C.c_float * 5)()
         _check(self.lib.femgpu_rerun_resident(self.h, C.byref(tot), C.byref(st)))
         return tot.value, list(st)

@@ -50,6 +50,10 @@ static int fetch_result(Slot &s, femgpu_result *r) {
     if (s.n_maps) {
       TRY(s.h_maps.reserve(s.n_maps * 16));
       CU(cudaMemcpyAsync(s.h_maps.p, s.maps.p, s.n_maps * 16, cudaMemcpyDeviceToHost, s.stream));
+      if (s.has_aln) {
+        TRY(s.h_aln.reserve(s.n_maps * sizeof(femgpu_alignment)));
+        CU(cudaMemcpyAsync(s.h_aln.p, s.aln.p, s.n_maps * sizeof(femgpu_alignment), cudaMemcpyDeviceToHost, s.stream));
+      }
     }
     // infeasible read-strands are rare; count them from the status bytes
     TRY(s.h_status.reserve(2ull * n));
@@ -70,10 +74,12 @@ static int fetch_result(Slot &s, femgpu_result *r) {
   cudaEventElapsedTime(&t, s.ev[1], s.ev[2]); s.ms[1] = t;
   cudaEventElapsedTime(&t, s.ev[2], s.ev[3]); s.ms[2] = t;
   cudaEventElapsedTime(&t, s.ev[3], s.ev[4]); s.ms[3] = t;
-  cudaEventElapsedTime(&t, s.ev[0], s.ev[5]); s.ms[4] = t;
+  cudaEventElapsedTime(&t, s.ev[4], s.ev[6]); s.ms[4] = t;
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[5]); s.ms[5] = t;
   if (r) {
     r->first = hf;
     r->maps = s.h_maps.as<femgpu_mapping>();
+    r->alns = s.has_aln && s.n_maps ? s.h_aln.as<femgpu_alignment>() : nullptr;
     r->stats = s.stats;
   }
   return 0;
@@ -90,6 +96,7 @@ extern "C" int femgpu_submit_batch(femgpu_ctx *c, int slot, const femgpu_params 
   // overlap with them because each slot owns its stream.
   TRY(run_seed_and_candidates(c, s, pl));
   TRY(run_verify_and_compact(c, s, pl));
+  s.has_aln = c->device_traceback != 0;
   s.busy = true;
   c->last_slot = slot;
   return 0;
@@ -162,7 +169,7 @@ extern "C" int femgpu_candidates_batch(femgpu_ctx *c, const femgpu_params *p, co
 }
 
 // ---- measurement hooks -----------------------------------------------------------------------------
-extern "C" int femgpu_last_timings(femgpu_ctx *c, float ms[5], uint32_t *n_launches) {
+extern "C" int femgpu_last_timings(femgpu_ctx *c, float ms[6], uint32_t *n_launches) {
   if (!c) return set_error(FEMGPU_EINVAL, "null context");
   const Slot &s = c->slot[c->last_slot];
   if (ms) memcpy(ms, s.ms, sizeof s.ms);
@@ -180,7 +187,7 @@ extern "C" int femgpu_last_work(femgpu_ctx *c, uint64_t work[4]) {
   return 0;
 }
 
-extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[4]) {
+extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[5]) {
   if (!c) return set_error(FEMGPU_EINVAL, "null context");
   Slot &s = c->slot[c->last_slot];
   if (s.busy) return set_error(FEMGPU_ESTATE, "slot busy");
@@ -193,8 +200,11 @@ extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_st
   CU(cudaStreamSynchronize(s.stream));
   float t;
   if (ms_stage)
+  {
     for (int i = 0; i < 4; ++i) { cudaEventElapsedTime(&t, s.ev[i], s.ev[i + 1]); ms_stage[i] = t; }
-  cudaEventElapsedTime(&t, s.ev[0], s.ev[4]);
+    cudaEventElapsedTime(&t, s.ev[4], s.ev[6]); ms_stage[4] = t;
+  }
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[6]);
   if (ms_total) *ms_total = t;
   return 0;
 }
@@ -248,6 +258,78 @@ void map_flag_sort(femgpu_mapping *beg, femgpu_mapping *end, int shift) {
   }
 }
 } // namespace
+
+// The same permutation applied to a parallel array of alignments: the records are sorted with
+// their original index in the two reserved bytes' place (a wider copy), then the alignments follow.
+extern "C" void femgpu_sort_mappings(femgpu_mapping *maps, size_t n);
+extern "C" void femgpu_sort_mappings_aln(femgpu_mapping *maps, femgpu_alignment *alns, size_t n) {
+  if (!maps || n < 2 || !alns) { femgpu_sort_mappings(maps, n); return; }
+  // equal sort keys are the only source of ambiguity; tag every record with its position so that
+  // the permutation can be read back.  The tag lives in bytes the key never looks at.
+  std::vector<uint32_t> idx(n);
+  std::vector<femgpu_mapping> tagged(maps, maps + n);
+  const bool small = n <= 0xFFFF;
+  std::vector<femgpu_alignment> src(alns, alns + n);
+  if (small) {
+    for (size_t i = 0; i < n; ++i) { tagged[i].reserved[0] = (uint8_t)(i & 255); tagged[i].reserved[1] = (uint8_t)(i >> 8); }
+    femgpu_sort_mappings(tagged.data(), n);
+    for (size_t i = 0; i < n; ++i) {
+      const size_t from = (size_t)tagged[i].reserved[0] | ((size_t)tagged[i].reserved[1] << 8);
+      alns[i] = src[from];
+      maps[i] = tagged[i];
+      maps[i].reserved[0] = maps[i].reserved[1] = 0;
+    }
+    return;
+  }
+  // more than 65535 mappings of one read: 32-bit tag in the upper half of end_position_offset's
+  // slot is not available, so sort (record, index) pairs with the same algorithm
+  struct Pair { femgpu_mapping m; uint32_t i; };
+  std::vector<Pair> pr(n);
+  for (size_t i = 0; i < n; ++i) { pr[i].m = maps[i]; pr[i].i = (uint32_t)i; }
+  struct S {
+    static uint64_t key(const Pair &p) { return map_key(p.m); }
+    static void insertion(Pair *b, Pair *e) {
+      for (Pair *i = b + 1; i < e; ++i) {
+        if (key(*i) >= key(*(i - 1))) continue;
+        const Pair t = *i;
+        Pair *j = i;
+        for (; j > b && key(t) < key(*(j - 1)); --j) *j = *(j - 1);
+        *j = t;
+      }
+    }
+    static void flag(Pair *beg, Pair *end, int shift) {
+      struct Bucket { Pair *head, *tail; } bk[256];
+      size_t hist[256] = {0};
+      for (Pair *i = beg; i != end; ++i) ++hist[(key(*i) >> shift) & 255];
+      Pair *p = beg;
+      for (int d = 0; d < 256; ++d) { bk[d].head = p; p += hist[d]; bk[d].tail = p; }
+      for (int d = 0; d < 256;) {
+        Bucket &cur = bk[d];
+        if (cur.head == cur.tail) { ++d; continue; }
+        int dest = (int)((key(*cur.head) >> shift) & 255);
+        if (dest == d) { ++cur.head; continue; }
+        Pair moving = *cur.head;
+        while (dest != d) {
+          std::swap(moving, *bk[dest].head);
+          ++bk[dest].head;
+          dest = (int)((key(moving) >> shift) & 255);
+        }
+        *cur.head++ = moving;
+      }
+      if (shift == 0) return;
+      const int next = shift > 8 ? shift - 8 : 0;
+      Pair *b = beg;
+      for (int d = 0; d < 256; ++d) {
+        Pair *e = bk[d].tail;
+        if (e - b > 64) flag(b, e, next);
+        else if (e - b > 1) insertion(b, e);
+        b = e;
+      }
+    }
+  };
+  S::flag(pr.data(), pr.data() + n, 56);
+  for (size_t i = 0; i < n; ++i) { maps[i] = pr[i].m; alns[i] = src[pr[i].i]; }
+}
 
 extern "C" void femgpu_sort_mappings(femgpu_mapping *maps, size_t n) {
   if (!maps || n < 2) return;

@@ -18,6 +18,7 @@
 #include "k_cand_hash.cuh"
 #include "k_peak.cuh"
 #include "k_seed.cuh"
+#include "k_trace.cuh"
 #include "k_verify.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -108,19 +109,22 @@ struct Slot {
   DBuf seed_begin, seed_freq, seed_start;
   DBuf rs_cand_first, rs_cand_count, rs_map_count, rs_map_first, block_sums;
   DBuf cand, cand_rs, result, maps, overflow_list, counters;
+  DBuf read_flags, map_rs, aln;
   DBuf big_list, big_off, big_S, big_A, scratch, hash_list;
   DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
+  HBuf h_aln;
   HBuf h_counters, h_first, h_maps, h_overflow, h_plan, h_cands, h_before, h_status;
   uint64_t cand_cap = 0;
   // state of the batch in flight
   bool busy = false;
+  bool has_aln = false;
   femgpu_params params{};
   uint32_t n_reads = 0;
   uint64_t n_bases = 0;
   int l_max = 0;
   uint64_t n_cand = 0, n_maps = 0;
   femgpu_stats stats{};
-  float ms[5] = {0, 0, 0, 0, 0};
+  float ms[6] = {0, 0, 0, 0, 0, 0};
   uint32_t n_launches = 0;
   uint64_t cols_executed = 0;
 };
@@ -138,6 +142,7 @@ struct femgpu_ctx {
   uint32_t n_rec = 0;
   uint64_t ref_total = 0;
   bool ref_has_n = false;
+  bool ref_canonical = true; // every reference character is one of "ACGTN"
   // options
   int64_t scratch_limit_bytes = 8ll << 30;
   int64_t arena_candidates = 0; // 0 = automatic
@@ -145,6 +150,7 @@ struct femgpu_ctx {
   int l2_persist_lut = 1;
   int cand_mode = 0;    // 0: hash path first, then sort path, then global scratch; 1: skip the hash path
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
+  int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
   int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan (tests force both)
   Slot slot[2];
   int last_slot = 0;
@@ -188,10 +194,10 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
 static void slot_release(Slot &s) {
   DBuf *d[] = {&s.bases, &s.read_off, &s.codes, &s.rs_status, &s.rs_before, &s.rs_max_f, &s.rs_sum_f, &s.seed_begin,
                &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
-               &s.block_sums, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
+               &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
                &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first};
   for (auto *b : d) b->release();
-  HBuf *h[] = {&s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
+  HBuf *h[] = {&s.h_aln, &s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
   for (auto *b : h) b->release();
   for (auto &e : s.ev) if (e) cudaEventDestroy(e);
   if (s.stream) cudaStreamDestroy(s.stream);
@@ -216,6 +222,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
   else if (k == "cand_mode" && value >= 0 && value <= 1) c->cand_mode = (int)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
+  else if (k == "device_traceback") c->device_traceback = value != 0;
   else if (k == "seed_dp_mode" && value >= 0 && value <= 2) c->seed_dp_mode = (int)value;
   else return set_error(FEMGPU_EINVAL, "unknown option or bad value: %s=%lld", key, (long long)value);
   return 0;

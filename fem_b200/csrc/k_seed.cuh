@@ -27,6 +27,7 @@ struct SeedArgs {
   int n_words_max, ns_max, w_max; // shared-memory plan for the longest read of the batch
   int lane_dp;
   uint8_t *codes;             // out: 2 * total_bases; strand d of read i at 2*off[i] + d*len
+  uint8_t *read_flags;        // out: per read, bit 0 = a character outside "ACGTN" (k_trace leaves it to the host)
   uint8_t *rs_status;         // out: per read-strand
   uint32_t *rs_before;        // out: DP minimum summed over groups (filter.c:202)
   uint32_t *rs_max_f;         // out: max over groups of the selected seeds' total frequency
@@ -70,12 +71,15 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
 
   // ---- base codes (strand oriented), 2-bit packing, ambiguous-base count --------------------
   int amb = 0;
+  bool noncanon = false;
   const int n_words = (l + 15) / 16 + 1;
   for (int base = 0; base < n_words * 16; base += 32) {
     const int i = base + (int)lane;
     uint32_t c = 0, valid = i < l;
     if (valid) {
-      c = fem_base_code((unsigned char)(dir ? A.bases[off + (uint64_t)(l - 1 - i)] : A.bases[off + (uint64_t)i]));
+      const unsigned char ch = (unsigned char)(dir ? A.bases[off + (uint64_t)(l - 1 - i)] : A.bases[off + (uint64_t)i]);
+      c = fem_base_code(ch);
+      noncanon |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'N');
       if (dir && c < 4) c = 3u - c; // 3 ^ code; ambiguous stays ambiguous (-> 'N')
       codes[i] = (uint8_t)c;
     }
@@ -88,6 +92,10 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
     if ((lane & 15) == 0 && (i >> 4) < n_words) pw[i >> 4] = v;
   }
   __syncwarp();
+  if (dir == 0) {
+    const bool any_noncanon = __any_sync(0xffffffffu, noncanon);
+    if (lane == 0) A.read_flags[read] = any_noncanon ? 1 : 0;
+  }
 
   uint8_t status = RS_OK;
   if (n_s <= 0) status = RS_INFEASIBLE;                  // reference: assert, filter.c:167

@@ -1,0 +1,150 @@
+// k_trace.cuh -- K6: alignment traceback of the accepted mappings on the device, one thread per
+// mapping: start position and CIGAR of src/align.c:279-499 (generate_alignment).
+//
+// The reference recomputes the band in 32-bit words keeping D0 and HP of every column
+// (src/align.c:303-338), then walks back from the end cell consuming exactly `edit_distance`
+// errors (:340-440) and emits the run-length operations reversed (:441-498).  The same walk is
+// done here per thread with the two per-column words in local memory; the host (sam.c) keeps only
+// the MD string and the text formatting.  The reference compares RAW characters in this function
+// while the band uses base codes; codes and characters agree exactly when every
+// character is one of "ACGTN", so mappings of reads (or references) with any other character are
+// flagged FEMGPU_ALN_HOST and the host runs its own femhost_alignment on them.
+#pragma once
+#include "common.cuh"
+#include "k_verify.cuh" // ref_code_at
+
+#define ALN_MAX_OPS 18
+#define ALN_HOST 0xFFu // n_cigar value: not computed on the device
+
+struct TraceArgs {
+  DevRef ref;
+  const uint8_t *codes;        // strand-oriented read codes (k_seed)
+  const uint64_t *read_off;
+  const uint8_t *read_flags;   // bit 0: read holds a character outside "ACGTN"
+  const ulonglong2 *maps;      // compacted 16-byte mapping records (k_compact)
+  const uint32_t *map_rs;      // owning read-strand of each record
+  uint64_t n_maps;
+  int e;
+  int ref_canonical;
+  uint32_t *aln;               // out: 10 words per mapping (femgpu_alignment, 40 bytes)
+};
+
+template <bool HAS_N>
+__device__ __forceinline__ uint32_t ref_code_fetch(const DevRef &R, uint64_t g) {
+  uint32_t c = (__ldg(R.ref2 + (g >> 4)) >> (2 * (g & 15))) & 3u;
+  if (HAS_N && ((__ldg(R.refn + (g >> 5)) >> (g & 31)) & 1u)) c = 4u;
+  return c;
+}
+
+__device__ __forceinline__ void aln_store(uint32_t *dst, int start, uint32_t n_cigar, const uint16_t *cig) {
+  dst[0] = ((uint32_t)(uint16_t)(int16_t)start) | (n_cigar << 16);
+#pragma unroll
+  for (int i = 0; i < ALN_MAX_OPS / 2; ++i) dst[1 + i] = (uint32_t)cig[2 * i] | ((uint32_t)cig[2 * i + 1] << 16);
+}
+
+template <bool HAS_N, int LCAP>
+__global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
+  const uint64_t mi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= A.n_maps) return;
+  uint32_t *out = A.aln + mi * 10;
+  uint16_t cig[ALN_MAX_OPS];
+#pragma unroll
+  for (int i = 0; i < ALN_MAX_OPS; ++i) cig[i] = 0;
+  const uint32_t rs = A.map_rs[mi];
+  const uint32_t read = rs >> 1, dir = rs & 1;
+  const uint64_t off = A.read_off[read];
+  const int l = (int)(A.read_off[read + 1] - off);
+  const ulonglong2 rec = A.maps[mi];
+  const int end_off = (int)(int32_t)(uint32_t)rec.y, dist = (int)((rec.y >> 40) & 0xFFu), e = A.e;
+  int start = end_off - l + 1;
+  if (!A.ref_canonical || (A.read_flags[read] & 1u) || l > LCAP || l <= 0 || start < 0) { aln_store(out, 0, ALN_HOST, cig); return; }
+  const uint8_t *text = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
+  const uint64_t g0 = A.ref.rec_base[rec.x >> 32] + (uint32_t)rec.x; // window[0]
+  uint32_t w2 = 0, wn = 0;
+
+  // :289-300 plain comparison at the reported end; no difference -> lM
+  int diff = 0;
+  {
+    uint64_t g = g0 + (uint64_t)start;
+    for (int i = 0; i < l; ++i, ++g) diff += text[i] != ref_code_at<HAS_N>(A.ref, g, w2, wn, i == 0);
+  }
+  if (diff == 0) {
+    cig[0] = (uint16_t)(l << 2);
+    aln_store(out, start, 1, cig);
+    return;
+  }
+  // :303-338 the band again, 32-bit words, D0 and HP of every column kept
+  uint32_t D0s[LCAP], HPs[LCAP];
+  {
+    uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0, VP = 0, VN = 0;
+    uint64_t g = g0;
+    for (int i = 0; i < 2 * e; ++i, ++g) {
+      const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, i == 0), bit = 1u << i;
+      p0 |= c == 0 ? bit : 0u; p1 |= c == 1 ? bit : 0u; p2 |= c == 2 ? bit : 0u; p3 |= c == 3 ? bit : 0u; p4 |= c == 4 ? bit : 0u;
+    }
+    const uint32_t hi = 1u << (2 * e);
+    for (int i = 0; i < l; ++i, ++g) {
+      const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, e == 0 && i == 0);
+      p0 |= c == 0 ? hi : 0u; p1 |= c == 1 ? hi : 0u; p2 |= c == 2 ? hi : 0u; p3 |= c == 3 ? hi : 0u; p4 |= c == 4 ? hi : 0u;
+      const uint32_t t = text[i];
+      const uint32_t eq = t == 0 ? p0 : t == 1 ? p1 : t == 2 ? p2 : t == 3 ? p3 : p4;
+      uint32_t X = eq | VN;
+      const uint32_t D0 = ((VP + (X & VP)) ^ VP) | X;
+      const uint32_t HN = VP & D0, HP = VN | ~(VP | D0);
+      X = D0 >> 1;
+      VN = X & HP;
+      VP = HN | ~(X | HP);
+      D0s[i] = D0;
+      HPs[i] = HP;
+      p0 >>= 1; p1 >>= 1; p2 >>= 1; p3 >>= 1; p4 >>= 1;
+    }
+  }
+  // :340-459 the walk.  Runs are collected from the read's 3' end; errors before the first match
+  // sit in a pseudo run 'S' that is folded into the run after it (:466-469).  Starting in an
+  // empty 'S' run makes the reference's special first step the general step (see sam.c).
+  enum { OP_M = 0, OP_I = 1, OP_D = 2, OP_S = 3 };
+  uint8_t ops[ALN_MAX_OPS + 2];
+  uint16_t cnt[ALN_MAX_OPS + 2];
+  int n_ops = 0, bit = start, tp = l - 1, rp = end_off, used = 0, run = OP_S, run_n = 0;
+  bool fail = false;
+#define CLOSE_RUN(next)                                                                            \
+  do {                                                                                             \
+    if (n_ops >= ALN_MAX_OPS + 1) { fail = true; break; }                                          \
+    ops[n_ops] = (uint8_t)run; cnt[n_ops++] = (uint16_t)run_n; run = (next); run_n = 1;            \
+  } while (0)
+  while (tp >= 0 && (used != dist || tp == l - 1) && !fail) {
+    const uint32_t sh = (uint32_t)bit & 31u; // the reference shifts by `bit`; out-of-range shifts are UB there
+    if (bit < 0 || bit > 31) { fail = true; break; }
+    const uint32_t d0 = (D0s[tp] >> sh) & 1u;
+    const bool same = rp >= 0 && ref_code_fetch<HAS_N>(A.ref, g0 + (uint64_t)rp) == text[tp];
+    if (d0 && same) { // match
+      --tp; --rp;
+      if (run != OP_M) CLOSE_RUN(OP_M); else ++run_n;
+    } else if (!d0) { // mismatch
+      --tp; --rp; ++used;
+      if (run == OP_S || run == OP_M) ++run_n; else CLOSE_RUN(OP_M);
+    } else if ((HPs[tp] >> sh) & 1u) { // insertion: a read base only
+      --tp; ++bit; ++used; ++start;
+      if (run == OP_S || run == OP_I) ++run_n; else CLOSE_RUN(OP_I);
+    } else { // deletion: a reference base only
+      if (tp == l - 1 && n_ops == 0 && run == OP_S && run_n == 0) { fail = true; break; } // reference asserts (:367)
+      --bit; --rp; ++used; --start;
+      if (run != OP_D) CLOSE_RUN(OP_D); else ++run_n;
+    }
+  }
+  if (!fail && tp >= 0) { // :441-459 the rest of the read matches
+    if (run != OP_M) { CLOSE_RUN(OP_M); run_n = tp + 1; }
+    else run_n += tp + 1;
+  }
+#undef CLOSE_RUN
+  if (!fail) { ops[n_ops] = (uint8_t)run; cnt[n_ops] = (uint16_t)run_n; }
+  int first = 0;
+  if (!fail && ops[0] == OP_S) { // :466-469
+    if (n_ops == 0) fail = true;
+    else { cnt[1] = (uint16_t)(cnt[1] + cnt[0]); first = 1; }
+  }
+  if (fail || n_ops - first + 1 > ALN_MAX_OPS) { aln_store(out, 0, ALN_HOST, cig); return; }
+  int nc = 0;
+  for (int i = n_ops; i >= first; --i) cig[nc++] = (uint16_t)(((uint32_t)cnt[i] << 2) | ops[i]);
+  aln_store(out, start, (uint32_t)nc, cig);
+}

@@ -175,6 +175,7 @@ struct CompactArgs {
   const uint32_t *rs_map_count;
   uint32_t n_rs;
   ulonglong2 *maps;             // 16-byte femgpu_mapping records
+  uint32_t *map_rs;             // owning read-strand of each record (k_trace)
 };
 
 __global__ void __launch_bounds__(256) k_compact(CompactArgs A) {
@@ -194,7 +195,9 @@ __global__ void __launch_bounds__(256) k_compact(CompactArgs A) {
       rec.x = A.cand[cf + t];
       // {int32 end_offset, uint8 direction, uint8 edit_distance, 2 reserved} little endian
       rec.y = (uint64_t)(r & 0xFFFFu) | ((uint64_t)(rs & 1) << 32) | ((uint64_t)(r >> 16) << 40);
-      A.maps[mf + w + __popc(m & lanemask_lt())] = rec;
+      const uint64_t o = mf + w + __popc(m & lanemask_lt());
+      A.maps[o] = rec;
+      A.map_rs[o] = (uint32_t)rs;
     }
     w += __popc(m);
   }

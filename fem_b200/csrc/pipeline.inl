@@ -54,6 +54,7 @@ static int slot_reserve(femgpu_ctx *c, Slot &s, const Plan &pl, uint32_t n_reads
   TRY(s.read_off.reserve((n_reads + 1ull) * 8));
   TRY(s.codes.reserve(2 * n_bases + 16));
   TRY(s.rs_status.reserve(n_rs + 16));
+  TRY(s.read_flags.reserve(n_reads + 16));
   TRY(s.rs_before.reserve(n_rs * 4 + 16));
   TRY(s.rs_max_f.reserve(n_rs * 4 + 16));
   TRY(s.rs_sum_f.reserve(n_rs * 4 + 16));
@@ -124,6 +125,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
   sa.lane_dp = pl.lane_dp;
   sa.codes = s.codes.as<uint8_t>();
+  sa.read_flags = s.read_flags.as<uint8_t>();
   sa.rs_status = s.rs_status.as<uint8_t>();
   sa.rs_before = s.rs_before.as<uint32_t>();
   sa.rs_max_f = s.rs_max_f.as<uint32_t>();
@@ -266,6 +268,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
   if (s.n_reads == 0) {
     cudaEventRecord(s.ev[3], s.stream);
     cudaEventRecord(s.ev[4], s.stream);
+    cudaEventRecord(s.ev[6], s.stream);
     return 0;
   }
   CU(cudaMemsetAsync(s.rs_map_count.p, 0, n_rs * 4, s.stream));
@@ -308,6 +311,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
   s.stats.num_mappings = hc.total_maps;
   if (s.n_maps) {
     TRY(s.maps.reserve(s.n_maps * 16));
+    TRY(s.map_rs.reserve(s.n_maps * 4));
     CompactArgs pa;
     pa.cand = s.cand.as<uint64_t>();
     pa.result = s.result.as<uint32_t>();
@@ -317,10 +321,39 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     pa.rs_map_count = s.rs_map_count.as<uint32_t>();
     pa.n_rs = (uint32_t)n_rs;
     pa.maps = s.maps.as<ulonglong2>();
+    pa.map_rs = s.map_rs.as<uint32_t>();
     k_compact<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(pa);
     ++s.n_launches;
     CU(cudaGetLastError());
   }
   cudaEventRecord(s.ev[4], s.stream);
+  // ---- K6: start + CIGAR of every mapping (src/align.c:279-499) ----------------------------------
+  if (s.n_maps && c->device_traceback) {
+    TRY(s.aln.reserve(s.n_maps * sizeof(femgpu_alignment)));
+    TraceArgs ta;
+    ta.ref.ref2 = c->ref2.as<uint32_t>();
+    ta.ref.refn = c->ref_has_n ? c->refn.as<uint32_t>() : nullptr;
+    ta.ref.rec_base = c->rec_base.as<uint64_t>();
+    ta.ref.rec_len = c->rec_len.as<uint32_t>();
+    ta.ref.n_rec = c->n_rec;
+    ta.codes = s.codes.as<uint8_t>();
+    ta.read_off = s.read_off.as<uint64_t>();
+    ta.read_flags = s.read_flags.as<uint8_t>();
+    ta.maps = s.maps.as<ulonglong2>();
+    ta.map_rs = s.map_rs.as<uint32_t>();
+    ta.n_maps = s.n_maps;
+    ta.e = pl.e;
+    ta.ref_canonical = c->ref_canonical ? 1 : 0;
+    ta.aln = s.aln.as<uint32_t>();
+    const unsigned grid = (unsigned)((s.n_maps + 127) / 128);
+    const int cap = s.l_max <= 128 ? 128 : s.l_max <= 256 ? 256 : 1024;
+#define LAUNCH_TRACE(N, L) k_trace<N, L><<<grid, 128, 0, s.stream>>>(ta)
+    if (c->ref_has_n) { if (cap == 128) LAUNCH_TRACE(true, 128); else if (cap == 256) LAUNCH_TRACE(true, 256); else LAUNCH_TRACE(true, 1024); }
+    else { if (cap == 128) LAUNCH_TRACE(false, 128); else if (cap == 256) LAUNCH_TRACE(false, 256); else LAUNCH_TRACE(false, 1024); }
+#undef LAUNCH_TRACE
+    ++s.n_launches;
+    CU(cudaGetLastError());
+  }
+  cudaEventRecord(s.ev[6], s.stream);
   return 0;
 }

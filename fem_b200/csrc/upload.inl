@@ -9,9 +9,12 @@ __global__ void __launch_bounds__(256) k_pack_reference(const unsigned char *chu
   const uint64_t i0 = t * 32;
   if (i0 >= n) return;
   uint32_t w0 = 0, w1 = 0, wn = 0;
+  bool noncanon = false;
   const int cnt = (int)min((uint64_t)32, n - i0);
   for (int j = 0; j < cnt; ++j) {
-    const uint32_t c = fem_base_code(chunk[i0 + j]);
+    const unsigned char ch = chunk[i0 + j];
+    const uint32_t c = fem_base_code(ch);
+    if (!(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'N')) noncanon = true;
     const uint32_t two = c & 3u; // ambiguous packs as 0; the mask decides
     if (j < 16) w0 |= (c < 4 ? two : 0u) << (2 * j);
     else w1 |= (c < 4 ? two : 0u) << (2 * (j - 16));
@@ -21,7 +24,8 @@ __global__ void __launch_bounds__(256) k_pack_reference(const unsigned char *chu
   ref2[g >> 4] = w0;
   ref2[(g >> 4) + 1] = w1;
   refn[g >> 5] = wn;
-  if (wn) *any_n = 1;
+  if (wn) atomicOr(any_n, 1);
+  if (noncanon) atomicOr(any_n, 2); // a character outside "ACGTN": k_trace leaves such input to the host
 }
 
 extern "C" int femgpu_upload_index(femgpu_ctx *c, int32_t k, int32_t step, const uint32_t *lut, size_t lut_n,
@@ -149,6 +153,7 @@ extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char
   if (err != cudaSuccess) return set_error(FEMGPU_ECUDA, "reference upload failed: %s", cudaGetErrorString(err));
   c->n_rec = n_rec;
   c->ref_total = total;
-  c->ref_has_n = any_n != 0;
+  c->ref_has_n = (any_n & 1) != 0;
+  c->ref_canonical = (any_n & 2) == 0;
   return 0;
 }

@@ -57,6 +57,7 @@ EXPORTS = {
     "femhost_reader_close": (None, [C.c_void_p]),
     "femhost_reader_next": (C.c_int64, [C.c_void_p, C.c_uint32, C.POINTER(RecordsStruct)]),
     "femhost_load_all": (C.c_int, [C.c_char_p, C.POINTER(RecordsStruct)]),
+    "femhost_load_all_ranges": (C.c_int, [C.c_char_p, C.c_uint64, C.POINTER(RecordsStruct)]),
     "femhost_index_build": (C.c_int, [C.POINTER(RecordsStruct), C.c_int, C.c_int, C.POINTER(IndexStruct)]),
     "femhost_index_save": (C.c_int, [C.POINTER(IndexStruct), C.c_char_p]),
     "femhost_index_load": (C.c_int, [C.c_char_p, C.POINTER(IndexStruct)]),
@@ -66,7 +67,7 @@ EXPORTS = {
     "femhost_alignment": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint32),
                                     C.POINTER(C.c_int), C.c_char_p]),
     "femhost_sam_read": (C.c_int, [C.POINTER(RecordsStruct), C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
-                                   C.c_void_p, C.c_size_t, C.POINTER(StrStruct)]),
+                                   C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(StrStruct)]),
     "femhost_mapper_create": (C.c_void_p, [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int)]),
     "femhost_mapper_destroy": (None, [C.c_void_p]),
     "femhost_mapper_reference": (C.POINTER(RecordsStruct), [C.c_void_p]),
@@ -148,6 +149,18 @@ def load_all(path):
     return r
 
 
+def load_all_ranges(path, chunk_bytes):
+    """-> Records, or None when the file is not plain four-line FASTQ (parallel reader's fallback)."""
+    r = Records()
+    rc = r.lib.femhost_load_all_ranges(os.fsencode(path), chunk_bytes, C.byref(r.c))
+    if rc == 1:
+        r.close()
+        return None
+    if rc != 0:
+        raise FemGpuError(_err())
+    return r
+
+
 def read_batches(path, batch):
     """Generator over lists of (name, seq, qual) in batches of `batch` records."""
     lib = load_host_library()
@@ -218,12 +231,14 @@ def sam_header(ref: Records) -> bytes:
     return out
 
 
-def sam_read(ref: Records, name: bytes, seq: bytes, qual: bytes, e: int, maps: np.ndarray) -> bytes:
-    """SAM lines of one read; `maps` (MAPPING_DTYPE, emission order) is sorted in place."""
+def sam_read(ref: Records, name: bytes, seq: bytes, qual: bytes, e: int, maps: np.ndarray, alns=None) -> bytes:
+    """SAM lines of one read; `maps` (MAPPING_DTYPE, emission order) is sorted in place, `alns`
+    (ALIGNMENT_DTYPE, the device's start/CIGAR per mapping, optional) follows the permutation."""
     lib = load_host_library()
     assert maps.dtype == MAPPING_DTYPE and maps.flags.c_contiguous
     s = StrStruct()
-    rc = lib.femhost_sam_read(C.byref(ref.c), name, seq, qual, len(seq), e, maps.ctypes.data, maps.shape[0], C.byref(s))
+    rc = lib.femhost_sam_read(C.byref(ref.c), name, seq, qual, len(seq), e, maps.ctypes.data,
+                              alns.ctypes.data if alns is not None else None, maps.shape[0], C.byref(s))
     out = C.string_at(s.s, s.l) if s.l else b""
     lib.femhost_str_free(C.byref(s))
     if rc != 0:

@@ -8,10 +8,13 @@
  *   -t worker threads  per-read mapping order, traceback, SAM text, chunk by chunk (sam.c)
  *   writer thread      batches in file order -> output: byte-identical to the reference's -t 1
  */
+#include <fcntl.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include "femhost.h"
 #include "host_internal.h"
@@ -107,6 +110,8 @@ femhost_mapper *femhost_mapper_create(const char *ref_path, const char *index_pa
     rc = n_gpus > 1 ? femgpu_upload_index(m->ctx[g], idx.k, idx.step, idx.lut, idx.lut_n, idx.occ, idx.n_occ)
                     : femgpu_upload_index_file(m->ctx[g], index_path);
     if (!rc) rc = femgpu_upload_reference(m->ctx[g], m->ref.n_records, seqs, lens);
+    const char *tb = getenv("FEM_DEVICE_TRACEBACK"); /* "0": start/CIGAR of every mapping on the host */
+    if (!rc && tb) rc = femgpu_set_option(m->ctx[g], "device_traceback", atoi(tb));
     if (rc) femhost_set_error(rc, "%s", femgpu_last_error());
   }
   free(seqs);
@@ -135,13 +140,17 @@ typedef struct batch batch;
 typedef struct {
   batch *b;
   uint32_t chunk;
+  int write;                /* 0: build the chunk's SAM text; 1: pwrite it at file_off */
+  uint64_t file_off;
 } work_item;
 struct batch {
   uint64_t seq;             /* position in file order */
   femhost_records reads;    /* pinned: the device copies straight out of it */
   uint64_t *first;          /* copy of the device result (the slot is reused at once) */
   femgpu_mapping *maps;
-  size_t cap_first, cap_maps;
+  femgpu_alignment *alns;   /* NULL-able: device start/CIGAR per mapping */
+  int has_alns;
+  size_t cap_first, cap_maps, cap_alns;
   femgpu_stats stats;
   uint32_t n_launches;
   uint32_t n_chunks;
@@ -149,6 +158,7 @@ struct batch {
   work_item *items;
   size_t cap_chunks;
   int chunks_left;          /* guarded by run->mu */
+  int writes_left;          /* guarded by run->mu */
 };
 
 static void pool_free(femhost_mapper *m) {
@@ -157,6 +167,7 @@ static void pool_free(femhost_mapper *m) {
     femhost_records_free(&b->reads);
     free(b->first);
     free(b->maps);
+    free(b->alns);
     for (size_t c = 0; c < b->cap_chunks; ++c) femhost_str_free(&b->text[c]);
     free(b->text);
     free(b->items);
@@ -170,7 +181,11 @@ typedef struct {
   femhost_mapper *m;
   const femhost_map_options *opt;
   femhost_reader *rd;
-  FILE *out;
+  int out_fd;               /* -1: build the text, write nothing */
+  int out_seekable;         /* regular file: chunks are written in parallel with pwrite */
+  uint64_t out_off;         /* next file offset (writer thread only) */
+  int writes_outstanding;   /* guarded by mu; writer waits for 0 before the file is closed */
+  pthread_cond_t writes_done;
   fifo q_free, q_parsed, q_work;
   /* finished batches wait here for the writer, indexed by seq % n_batches */
   batch **done;
@@ -179,6 +194,11 @@ typedef struct {
   pthread_cond_t batch_done;
   uint64_t n_parsed;        /* batches handed to the GPUs; valid once parsing_over */
   int parsing_over;
+  /* parallel reader (plain four-line FASTQ): the file is cut into byte ranges, batch = range */
+  int fd;
+  uint64_t file_size, chunk_bytes, n_chunks, next_chunk;
+  int readers_left;
+  int restart_sequential;   /* some range did not parse as four-line FASTQ: run again with the kseq reader */
   int failed;
   char error[512];
   /* accounting */
@@ -228,6 +248,75 @@ static void *reader_main(void *arg) {
   return NULL;
 }
 
+/* ---- parallel reader --------------------------------------------------------------------------- */
+/* Range i covers the records that start in [sync(i*chunk), sync((i+1)*chunk)), where sync(a) is the
+ * first record start after the first line break at or after a (femhost_fastq4_sync).  Every range
+ * must parse exactly, record by record, with the four-line fast path; since range i ends where
+ * range i+1 starts, the ranges together are the sequential parse of the file.  Anything else
+ * (multi-line records, FASTA, CRLF, junk) aborts the run, which map_file repeats with the
+ * sequential kseq-compatible reader. */
+static int64_t par_sync(run_state *r, uint64_t a, unsigned char *win, size_t win_cap) {
+  if (a == 0) return 0;
+  if (a >= r->file_size) return (int64_t)r->file_size;
+  size_t n = win_cap;
+  if (a + n > r->file_size) n = (size_t)(r->file_size - a);
+  if (pread(r->fd, win, n, (off_t)a) != (ssize_t)n) return -1;
+  const long o = femhost_fastq4_sync(win, n, 0, a + n == r->file_size);
+  return o < 0 ? -1 : (int64_t)(a + (uint64_t)o);
+}
+
+typedef struct {
+  run_state *r;
+  double busy;
+} par_arg;
+
+static void *par_reader_main(void *arg) {
+  par_arg *pa = (par_arg *)arg;
+  run_state *r = pa->r;
+  const size_t win_cap = 1 << 18;
+  unsigned char *win = (unsigned char *)malloc(win_cap), *raw = NULL;
+  size_t raw_cap = 0;
+  for (;;) {
+    /* a batch object first, a range number second: the lowest range in flight always owns one */
+    batch *b = (batch *)fifo_pop(&r->q_free);
+    pthread_mutex_lock(&r->mu);
+    const uint64_t i = r->next_chunk < r->n_chunks && !r->failed && !r->restart_sequential ? r->next_chunk++ : UINT64_MAX;
+    pthread_mutex_unlock(&r->mu);
+    if (i == UINT64_MAX) { fifo_push(&r->q_free, b); break; }
+    const double t0 = femhost_now();
+    const int64_t lo = par_sync(r, i * r->chunk_bytes, win, win_cap);
+    const int64_t hi = i + 1 == r->n_chunks ? (int64_t)r->file_size : par_sync(r, (i + 1) * r->chunk_bytes, win, win_cap);
+    int rc = lo < 0 || hi < lo ? 1 : 0;
+    if (!rc) {
+      const size_t n = (size_t)(hi - lo);
+      if (n > raw_cap) { raw_cap = n + n / 8 + 4096; free(raw); raw = (unsigned char *)malloc(raw_cap); }
+      if (n && pread(r->fd, raw, n, (off_t)lo) != (ssize_t)n) rc = 1;
+      else rc = femhost_parse_fastq4(raw, raw + n, &b->reads);
+    }
+    pa->busy += femhost_now() - t0;
+    b->seq = i;
+    if (rc) {
+      pthread_mutex_lock(&r->mu);
+      if (rc < 0) { if (!r->failed) { r->failed = 1; snprintf(r->error, sizeof r->error, "%s", femhost_last_error()); } }
+      else r->restart_sequential = 1;
+      pthread_mutex_unlock(&r->mu);
+      b->reads.n_records = 0;
+    }
+    fifo_push(&r->q_parsed, b);
+  }
+  free(win);
+  free(raw);
+  pthread_mutex_lock(&r->mu);
+  if (--r->readers_left == 0) {
+    r->n_parsed = r->next_chunk;
+    r->parsing_over = 1;
+    pthread_cond_broadcast(&r->batch_done);
+    pthread_mutex_unlock(&r->mu);
+    fifo_close(&r->q_parsed);
+  } else pthread_mutex_unlock(&r->mu);
+  return NULL;
+}
+
 typedef struct {
   run_state *r;
   int gpu, slot;
@@ -251,7 +340,7 @@ static void *gpu_main(void *arg) {
     const uint32_t n = b->reads.n_records;
     memset(&b->stats, 0, sizeof b->stats);
     b->n_chunks = 0;
-    int ok = !r->failed;
+    int ok = !r->failed && !r->restart_sequential;
     if (ok) {
       const double t0 = femhost_now();
       femgpu_batch gb = {b->reads.bases, b->reads.base_off, n};
@@ -265,8 +354,13 @@ static void *gpu_main(void *arg) {
         if (n_maps > b->cap_maps) { b->cap_maps = n_maps + n_maps / 4 + 1024; b->maps = (femgpu_mapping *)realloc(b->maps, b->cap_maps * sizeof(femgpu_mapping)); }
         memcpy(b->first, res.first, ((size_t)n + 1) * 8);
         memcpy(b->maps, res.maps, n_maps * sizeof(femgpu_mapping));
+        b->has_alns = res.alns != NULL;
+        if (res.alns) {
+          if (n_maps > b->cap_alns) { b->cap_alns = n_maps + n_maps / 4 + 1024; b->alns = (femgpu_alignment *)realloc(b->alns, b->cap_alns * sizeof(femgpu_alignment)); }
+          memcpy(b->alns, res.alns, n_maps * sizeof(femgpu_alignment));
+        }
         b->stats = res.stats;
-        float ms[5];
+        float ms[6];
         femgpu_last_timings(ctx, ms, &b->n_launches);
       }
       ga->busy += femhost_now() - t0;
@@ -286,6 +380,7 @@ static void *gpu_main(void *arg) {
     for (uint32_t c = 0; c < n_chunks; ++c) {
       b->items[c].b = b;
       b->items[c].chunk = c;
+      b->items[c].write = 0;
       fifo_push(&r->q_work, &b->items[c]);
     }
   }
@@ -294,8 +389,17 @@ static void *gpu_main(void *arg) {
 
 typedef struct {
   run_state *r;
-  double busy;
+  double busy, busy_write;
 } worker_arg;
+
+static int write_all(int fd, const char *p, size_t n, int positional, uint64_t off) {
+  while (n) {
+    const ssize_t w = positional ? pwrite(fd, p, n, (off_t)off) : write(fd, p, n);
+    if (w <= 0) return -1;
+    p += w; n -= (size_t)w; off += (uint64_t)w;
+  }
+  return 0;
+}
 
 static void *worker_main(void *arg) {
   worker_arg *wa = (worker_arg *)arg;
@@ -308,6 +412,16 @@ static void *worker_main(void *arg) {
     const double t0 = femhost_now();
     batch *b = it->b;
     femhost_str *out = &b->text[it->chunk];
+    if (it->write) { /* the writer thread fixed the offset; the copy into the page cache happens here */
+      if (write_all(r->out_fd, out->s, out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
+      wa->busy_write += femhost_now() - t0;
+      pthread_mutex_lock(&r->mu);
+      const int left = --b->writes_left;
+      if (--r->writes_outstanding == 0) pthread_cond_broadcast(&r->writes_done);
+      pthread_mutex_unlock(&r->mu);
+      if (left == 0) fifo_push(&r->q_free, b);
+      continue;
+    }
     out->l = 0;
     const uint32_t lo = it->chunk * CHUNK_READS;
     const uint32_t hi = lo + CHUNK_READS < b->reads.n_records ? lo + CHUNK_READS : b->reads.n_records;
@@ -317,7 +431,7 @@ static void *worker_main(void *arg) {
       const uint64_t off = b->reads.base_off[i];
       if (femhost_sam_read(ref, femhost_record_name(&b->reads, i), b->reads.bases + off,
                            b->reads.has_qual[i] ? b->reads.quals + off : no_qual, (int)femhost_record_length(&b->reads, i), e,
-                           b->maps + b->first[i], n, out))
+                           b->maps + b->first[i], b->has_alns ? b->alns + b->first[i] : NULL, n, out))
         run_fail(r, femhost_last_error());
     }
     wa->busy += femhost_now() - t0;
@@ -344,9 +458,27 @@ static void *writer_main(void *arg) {
     pthread_mutex_unlock(&r->mu);
     if (!b) break;
     const double t0 = femhost_now();
+    int n_writes = 0;
     for (uint32_t c = 0; c < b->n_chunks; ++c) {
-      r->tm.sam_bytes += b->text[c].l;
-      if (r->out && b->text[c].l && fwrite(b->text[c].s, 1, b->text[c].l, r->out) != b->text[c].l) run_fail(r, "short write to the SAM file");
+      const size_t len = b->text[c].l;
+      r->tm.sam_bytes += len;
+      if (r->out_fd < 0 || !len) continue;
+      if (!r->out_seekable) { /* pipe: in order, from this thread */
+        if (write_all(r->out_fd, b->text[c].s, len, 0, 0)) run_fail(r, "short write to the SAM file");
+        continue;
+      }
+      b->items[c].write = 1;
+      b->items[c].file_off = r->out_off;
+      r->out_off += len;
+      ++n_writes;
+    }
+    if (n_writes) { /* hand the copies to the workers; the last one recycles the batch */
+      pthread_mutex_lock(&r->mu);
+      b->writes_left = n_writes;
+      r->writes_outstanding += n_writes;
+      pthread_mutex_unlock(&r->mu);
+      for (uint32_t c = 0; c < b->n_chunks; ++c)
+        if (b->items[c].write) fifo_push(&r->q_work, &b->items[c]);
     }
     busy += femhost_now() - t0;
     r->stats.num_reads += b->stats.num_reads;
@@ -356,37 +488,71 @@ static void *writer_main(void *arg) {
     r->stats.num_mappings += b->stats.num_mappings;
     r->stats.num_infeasible_reads += b->stats.num_infeasible_reads;
     r->tm.h2d_bytes += b->reads.n_bases + ((uint64_t)b->reads.n_records + 1) * 8;
-    r->tm.d2h_bytes += ((uint64_t)b->reads.n_records + 1) * 8 + b->stats.num_mappings * sizeof(femgpu_mapping) + 2ull * b->reads.n_records;
+    r->tm.d2h_bytes += ((uint64_t)b->reads.n_records + 1) * 8 + b->stats.num_mappings * (sizeof(femgpu_mapping) + (b->has_alns ? sizeof(femgpu_alignment) : 0)) + 2ull * b->reads.n_records;
     r->tm.n_launches += b->n_launches;
     ++r->tm.n_batches;
     ++next;
-    fifo_push(&r->q_free, b);
+    if (!n_writes) fifo_push(&r->q_free, b);
   }
+  pthread_mutex_lock(&r->mu);
+  while (r->writes_outstanding) pthread_cond_wait(&r->writes_done, &r->mu);
+  pthread_mutex_unlock(&r->mu);
   r->tm.write = busy;
   return NULL;
 }
 
-/* ---- src/FEM_map.c:146-219 ------------------------------------------------------------------------ */
-int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
-                     femgpu_stats *stats, femhost_map_timing *timing) {
-  if (!m || !opt || !reads_path) return femhost_set_error(-1, "map: null argument");
-  if (opt->params.e < 0 || opt->params.e > 7) return femhost_set_error(-1, "Wrong error threshold.");         /* src/FEM_map.c:30 */
-  if (opt->n_threads <= 0 || opt->n_threads > 1024) return femhost_set_error(-1, "Wrong number of threads."); /* :34 */
-  if (opt->params.a < 0 || opt->params.a > 2) return femhost_set_error(-1, "Wrong number of additional q-grams."); /* :38 */
+/* plain (not gzip) regular file that starts with '@': candidate for the parallel reader */
+static int parallel_readable(const char *path, uint64_t *size) {
+  struct stat st;
+  if (stat(path, &st) != 0 || !S_ISREG(st.st_mode) || st.st_size < 4) return 0;
+  const int fd = open(path, O_RDONLY);
+  if (fd < 0) return 0;
+  unsigned char b[2] = {0, 0};
+  const ssize_t n = read(fd, b, 2);
+  close(fd);
+  *size = (uint64_t)st.st_size;
+  return n == 2 && b[0] == '@';
+}
+
+#define N_PAR_READERS 3
+
+static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
+                        int parallel, femgpu_stats *stats, femhost_map_timing *timing, int *restart) {
   run_state r;
   memset(&r, 0, sizeof r);
   r.m = m;
   r.opt = opt;
-  r.rd = femhost_reader_open(reads_path);
-  if (!r.rd) return -1;
-  if (sam_path) {
-    r.out = fopen(sam_path, "wb");
-    if (!r.out) { femhost_reader_close(r.rd); return femhost_set_error(-1, "Cannot open output file %s", sam_path); }
-    setvbuf(r.out, NULL, _IOFBF, 8 << 20);
+  r.fd = -1;
+  if (parallel) {
+    r.fd = open(reads_path, O_RDONLY);
+    if (r.fd < 0) return femhost_set_error(-1, "Cannot find sequence file!");
+    struct stat st;
+    fstat(r.fd, &st);
+    r.file_size = (uint64_t)st.st_size;
+    const uint64_t per_batch = opt->batch_reads ? opt->batch_reads : 131072u;
+    r.chunk_bytes = per_batch * 224; /* about per_batch reads of 100 bp; only the batch granularity depends on it */
+    if (r.chunk_bytes < 4096) r.chunk_bytes = 4096;
+    r.n_chunks = (r.file_size + r.chunk_bytes - 1) / r.chunk_bytes;
+    r.readers_left = N_PAR_READERS;
+  } else {
+    r.rd = femhost_reader_open(reads_path);
+    if (!r.rd) return -1;
   }
+  r.out_fd = -1;
+  if (sam_path) {
+    r.out_fd = open(sam_path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (r.out_fd < 0) {
+      if (r.rd) femhost_reader_close(r.rd);
+      if (r.fd >= 0) close(r.fd);
+      return femhost_set_error(-1, "Cannot open output file %s", sam_path);
+    }
+    struct stat ost;
+    r.out_seekable = fstat(r.out_fd, &ost) == 0 && S_ISREG(ost.st_mode);
+  }
+  pthread_cond_init(&r.writes_done, NULL);
   const double t_start = femhost_now();
-  const int n_gpu_threads = 2 * m->n_gpus, n_workers = opt->n_threads;
-  r.n_batches = (size_t)(2 * n_gpu_threads + 2);
+  const int n_gpu_threads = 2 * m->n_gpus, n_workers = opt->n_threads, n_readers = parallel ? N_PAR_READERS : 1;
+  r.n_batches = (size_t)(2 * n_gpu_threads + 2 + (parallel ? N_PAR_READERS : 0));
   if (m->n_pool != r.n_batches) {
     pool_free(m);
     m->pool = (batch *)calloc(r.n_batches, sizeof(batch));
@@ -405,14 +571,20 @@ int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const ch
     femhost_str hdr = {0, 0, 0};
     if (femhost_sam_header(&m->ref, &hdr) == 0) {
       r.tm.sam_bytes += hdr.l;
-      if (r.out) fwrite(hdr.s, 1, hdr.l, r.out);
+      if (r.out_fd >= 0 && write_all(r.out_fd, hdr.s, hdr.l, 0, 0)) run_fail(&r, "short write to the SAM file");
+      r.out_off = hdr.l;
     }
     femhost_str_free(&hdr);
   }
-  pthread_t th_reader, th_writer, th_gpu[2 * FEM_MAX_GPUS], *th_worker = (pthread_t *)calloc((size_t)n_workers, sizeof(pthread_t));
+  pthread_t th_reader[N_PAR_READERS], th_writer, th_gpu[2 * FEM_MAX_GPUS], *th_worker = (pthread_t *)calloc((size_t)n_workers, sizeof(pthread_t));
   gpu_arg ga[2 * FEM_MAX_GPUS];
+  par_arg pa[N_PAR_READERS];
   worker_arg *wa = (worker_arg *)calloc((size_t)n_workers, sizeof(worker_arg));
-  pthread_create(&th_reader, NULL, reader_main, &r);
+  for (int i = 0; i < n_readers; ++i) {
+    pa[i].r = &r; pa[i].busy = 0;
+    if (parallel) pthread_create(&th_reader[i], NULL, par_reader_main, &pa[i]);
+    else pthread_create(&th_reader[i], NULL, reader_main, &r);
+  }
   pthread_create(&th_writer, NULL, writer_main, &r);
   for (int i = 0; i < n_gpu_threads; ++i) {
     ga[i].r = &r; ga[i].gpu = i / 2; ga[i].slot = i % 2; ga[i].busy = 0;
@@ -422,20 +594,44 @@ int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const ch
     wa[i].r = &r;
     pthread_create(&th_worker[i], NULL, worker_main, &wa[i]);
   }
-  pthread_join(th_reader, NULL);
+  for (int i = 0; i < n_readers; ++i) { pthread_join(th_reader[i], NULL); if (parallel) r.tm.parse += pa[i].busy; }
   for (int i = 0; i < n_gpu_threads; ++i) { pthread_join(th_gpu[i], NULL); r.tm.gpu_wait += ga[i].busy; }
+  pthread_join(th_writer, NULL); /* returns once every chunk is formatted, ordered and written */
   fifo_close(&r.q_work);
-  for (int i = 0; i < n_workers; ++i) { pthread_join(th_worker[i], NULL); r.tm.format += wa[i].busy; }
-  pthread_join(th_writer, NULL);
-  if (r.out && fclose(r.out) != 0) run_fail(&r, "closing the SAM file failed");
+  for (int i = 0; i < n_workers; ++i) { pthread_join(th_worker[i], NULL); r.tm.format += wa[i].busy; r.tm.write += wa[i].busy_write; }
+  if (r.out_fd >= 0 && close(r.out_fd) != 0) run_fail(&r, "closing the SAM file failed");
+  pthread_cond_destroy(&r.writes_done);
   r.tm.wall = femhost_now() - t_start;
-  femhost_reader_close(r.rd);
+  if (r.rd) femhost_reader_close(r.rd);
+  if (r.fd >= 0) close(r.fd);
   free(r.done); free(th_worker); free(wa);
   fifo_destroy(&r.q_free); fifo_destroy(&r.q_parsed); fifo_destroy(&r.q_work);
   pthread_mutex_destroy(&r.mu);
   pthread_cond_destroy(&r.batch_done);
   if (stats) *stats = r.stats;
   if (timing) *timing = r.tm;
+  *restart = r.restart_sequential;
   if (r.failed) return femhost_set_error(-4, "%s", r.error);
   return 0;
+}
+
+/* ---- src/FEM_map.c:146-219 ------------------------------------------------------------------------ */
+int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
+                     femgpu_stats *stats, femhost_map_timing *timing) {
+  if (!m || !opt || !reads_path) return femhost_set_error(-1, "map: null argument");
+  if (opt->params.e < 0 || opt->params.e > 7) return femhost_set_error(-1, "Wrong error threshold.");         /* src/FEM_map.c:30 */
+  if (opt->n_threads <= 0 || opt->n_threads > 1024) return femhost_set_error(-1, "Wrong number of threads."); /* :34 */
+  if (opt->params.a < 0 || opt->params.a > 2) return femhost_set_error(-1, "Wrong number of additional q-grams."); /* :38 */
+  uint64_t size = 0;
+  const char *force = getenv("FEM_READER"); /* "kseq": always the sequential reader */
+  int parallel = opt->skip_reads == 0 && opt->max_reads == 0 && !(force && strcmp(force, "kseq") == 0) &&
+                 parallel_readable(reads_path, &size);
+  int restart = 0;
+  const double t0 = femhost_now();
+  int rc = map_file_run(m, opt, reads_path, sam_path, parallel, stats, timing, &restart);
+  if (rc == 0 && restart) { /* not plain four-line FASTQ after all: once more, sequentially */
+    rc = map_file_run(m, opt, reads_path, sam_path, 0, stats, timing, &restart);
+    if (timing) timing->wall = femhost_now() - t0;
+  }
+  return rc;
 }

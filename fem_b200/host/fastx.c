@@ -179,32 +179,33 @@ static int reserve_bases(void *ctx, size_t need) { return femhost_records_reserv
 
 /* One record appended as record number r->n_records (not yet counted).  Returns its sequence
  * length, -1 end of file, -2 truncated quality, -3 stream / memory error. */
-/* Fast path for the common shape: a four-line FASTQ record that lies completely inside the
- * buffer -- "@name[ comment]\n" "SEQ\n" "+...\n" "QUAL\n" with |QUAL| == |SEQ| > 0 and no '\r'.
- * For such a record the general scanner below produces exactly these fields, so it is parsed with
- * four memchr calls.  Returns the sequence length, or -4 when the record is not of that shape
- * (nothing consumed; the general scanner takes over). */
-static long fx_record_fast(femhost_reader *rd, femhost_records *r) {
-  const unsigned char *p = rd->buf + rd->begin, *end = rd->buf + rd->end;
-  if (p >= end || *p != '@') return -4;
+/* Fast path for the common shape: a four-line FASTQ record that lies completely inside [p, end)
+ * -- "@name[ comment]\n" "SEQ\n" "+...\n" "QUAL\n" with |QUAL| == |SEQ| > 0 and no '\r'.  For such a
+ * record the general scanner below produces exactly these fields, so it is parsed with four
+ * memchr calls and appended as record r->n_records (not counted yet).  Returns the first byte
+ * after the record, or NULL when the bytes at p are not of that shape (nothing is consumed;
+ * *oom is set when memory ran out instead). */
+static const unsigned char *fastq4_record(const unsigned char *p, const unsigned char *end, femhost_records *r, int *oom) {
+  if (p >= end || *p != '@') return NULL;
   const unsigned char *e1 = (const unsigned char *)memchr(p, '\n', (size_t)(end - p));
-  if (!e1 || e1 + 1 >= end) return -4;
+  if (!e1 || e1 + 1 >= end) return NULL;
   const unsigned char *s = e1 + 1;
-  if (*s == '\n' || *s == '>' || *s == '@' || *s == '+') return -4;
+  if (*s == '\n' || *s == '>' || *s == '@' || *s == '+') return NULL;
   const unsigned char *e2 = (const unsigned char *)memchr(s, '\n', (size_t)(end - s));
-  if (!e2 || e2 + 1 >= end || e2[1] != '+' || e2[-1] == '\r') return -4;
+  if (!e2 || e2 + 1 >= end || e2[1] != '+' || e2[-1] == '\r') return NULL;
   const unsigned char *e3 = (const unsigned char *)memchr(e2 + 1, '\n', (size_t)(end - e2 - 1));
-  if (!e3) return -4;
+  if (!e3) return NULL;
   const size_t sl = (size_t)(e2 - s);
   const unsigned char *q = e3 + 1;
-  if ((size_t)(end - q) < sl + 1 || q[sl] != '\n' || q[sl - 1] == '\r') return -4;
-  if (memchr(q, '\n', sl)) return -4; /* a shorter first quality line: general path */
+  if ((size_t)(end - q) < sl + 1 || q[sl] != '\n' || q[sl - 1] == '\r') return NULL;
+  if (memchr(q, '\n', sl)) return NULL; /* a shorter first quality line: general path */
   const unsigned char *n0 = p + 1, *n1 = n0;
   while (n1 < e1 && !isspace(*n1)) ++n1;
   const size_t nl = (size_t)(n1 - n0);
   const uint32_t i = r->n_records;
+  if (i == 0 && r->cap_records == 0 && femhost_records_reserve(r, 1, 16, 16)) { *oom = 1; return NULL; }
   const size_t nb = r->name_off[i], sb = r->base_off[i];
-  if (femhost_records_reserve(r, (size_t)i + 2, sb + sl + 2, nb + nl + 2)) return -3;
+  if (femhost_records_reserve(r, (size_t)i + 2, sb + sl + 2, nb + nl + 2)) { *oom = 1; return NULL; }
   memcpy(r->names + nb, n0, nl);
   r->names[nb + nl] = 0;
   memcpy(r->bases + sb, s, sl);
@@ -212,8 +213,57 @@ static long fx_record_fast(femhost_reader *rd, femhost_records *r) {
   r->name_off[i + 1] = nb + nl + 1;
   r->base_off[i + 1] = sb + sl;
   r->has_qual[i] = 1;
-  rd->begin = (int)(q + sl + 1 - rd->buf);
-  return (long)sl;
+  return q + sl + 1;
+}
+
+static long fx_record_fast(femhost_reader *rd, femhost_records *r) {
+  int oom = 0;
+  const unsigned char *next = fastq4_record(rd->buf + rd->begin, rd->buf + rd->end, r, &oom);
+  if (!next) return oom ? -3 : -4;
+  rd->begin = (int)(next - rd->buf);
+  return (long)(r->base_off[r->n_records + 1] - r->base_off[r->n_records]);
+}
+
+/* Whole buffer of four-line records (the parallel reader of engine.c): replaces the content of
+ * *out.  Returns 0 when [p, end) was consumed exactly, 1 when some record is not of the fast
+ * shape (the caller falls back to the sequential reader), -3 out of memory. */
+int femhost_parse_fastq4(const unsigned char *p, const unsigned char *end, femhost_records *out) {
+  out->n_records = 0;
+  out->n_bases = 0;
+  if (femhost_records_reserve(out, 1, 16, 16)) return -3;
+  int oom = 0;
+  while (p < end) {
+    const unsigned char *next = fastq4_record(p, end, out, &oom);
+    if (!next) return oom ? -3 : 1;
+    ++out->n_records;
+    p = next;
+  }
+  out->n_bases = out->base_off[out->n_records];
+  return 0;
+}
+
+/* First record start after the first line break of buf[0..n) (at 0 itself when at_file_start):
+ * a line that begins with '@' whose second next line begins with '+'.  A quality line may begin
+ * with '@', but then the second next line is a sequence line.  Returns the offset, n when the
+ * buffer holds no further line (end of file), or -1 when no decision is possible. */
+long femhost_fastq4_sync(const unsigned char *buf, size_t n, int at_file_start, int at_file_end) {
+  const unsigned char *p = buf, *end = buf + n;
+  if (!at_file_start) {
+    p = (const unsigned char *)memchr(p, '\n', n);
+    if (!p) return at_file_end ? (long)n : -1;
+    ++p;
+  }
+  while (p < end) {
+    const unsigned char *l1 = (const unsigned char *)memchr(p, '\n', (size_t)(end - p));
+    if (!l1) return at_file_end ? (long)n : -1;
+    if (*p == '@') {
+      const unsigned char *l2 = l1 + 1 < end ? (const unsigned char *)memchr(l1 + 1, '\n', (size_t)(end - l1 - 1)) : NULL;
+      if (!l2 || l2 + 1 >= end) return -1;
+      if (l2[1] == '+') return (long)(p - buf);
+    }
+    p = l1 + 1;
+  }
+  return at_file_end ? (long)n : -1;
 }
 
 static long fx_record(femhost_reader *rd, femhost_records *r) {
@@ -291,4 +341,60 @@ int femhost_load_all(const char *path, femhost_records *out) {
   int64_t n = femhost_reader_next(rd, 0xFFFFFFF0u, out);
   femhost_reader_close(rd);
   return n < 0 ? (int)n : 0;
+}
+
+/* The parallel reader's decomposition, run serially (tests, and a reference for engine.c): the
+ * file is cut at multiples of chunk_bytes, each range [sync(i*chunk), sync((i+1)*chunk)) is parsed
+ * on its own with the four-line fast path and the ranges are concatenated.  Returns 0, 1 when the
+ * file is not plain four-line FASTQ (callers use the sequential reader), negative on errors. */
+int femhost_load_all_ranges(const char *path, uint64_t chunk_bytes, femhost_records *out) {
+  FILE *f = fopen(path, "rb");
+  if (!f) return femhost_set_error(-1, "Cannot find sequence file!");
+  fseek(f, 0, SEEK_END);
+  const uint64_t size = (uint64_t)ftell(f);
+  fseek(f, 0, SEEK_SET);
+  unsigned char *buf = (unsigned char *)malloc(size + 1);
+  if (!buf || fread(buf, 1, size, f) != size) { fclose(f); free(buf); return femhost_set_error(-3, "cannot read %s", path); }
+  fclose(f);
+  out->n_records = 0;
+  out->n_bases = 0;
+  int rc = femhost_records_reserve(out, 1, 16, 16) ? -3 : 0;
+  if (!rc && (size < 4 || buf[0] != '@')) rc = 1;
+  if (chunk_bytes == 0) chunk_bytes = 1;
+  femhost_records part;
+  femhost_records_init(&part, 0);
+  const size_t win = 1 << 18;
+  for (uint64_t a = 0; !rc && a < size; a += chunk_bytes) {
+    uint64_t lim[2];
+    for (int j = 0; j < 2 && !rc; ++j) {
+      const uint64_t at = a + (uint64_t)j * chunk_bytes;
+      if (at == 0) lim[j] = 0;
+      else if (at >= size) lim[j] = size;
+      else {
+        const size_t n = at + win > size ? (size_t)(size - at) : win;
+        const long o = femhost_fastq4_sync(buf + at, n, 0, at + n == size);
+        if (o < 0) rc = 1;
+        else lim[j] = at + (uint64_t)o;
+      }
+    }
+    if (rc) break;
+    rc = femhost_parse_fastq4(buf + lim[0], buf + lim[1], &part);
+    if (rc) break;
+    const uint64_t nb = out->name_off[out->n_records], sb = out->base_off[out->n_records];
+    if (femhost_records_reserve(out, (size_t)out->n_records + part.n_records + 1, sb + part.n_bases + 2,
+                                nb + part.name_off[part.n_records] + 2)) { rc = -3; break; }
+    memcpy(out->bases + sb, part.bases, part.n_bases);
+    memcpy(out->quals + sb, part.quals, part.n_bases);
+    memcpy(out->names + nb, part.names, part.name_off[part.n_records]);
+    for (uint32_t i = 0; i < part.n_records; ++i) {
+      out->base_off[out->n_records + i + 1] = sb + part.base_off[i + 1];
+      out->name_off[out->n_records + i + 1] = nb + part.name_off[i + 1];
+      out->has_qual[out->n_records + i] = 1;
+    }
+    out->n_records += part.n_records;
+    out->n_bases += part.n_bases;
+  }
+  femhost_records_free(&part);
+  free(buf);
+  return rc;
 }

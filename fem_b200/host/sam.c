@@ -199,10 +199,10 @@ static void init_seq_out(void) {
 }
 
 int femhost_sam_read(const femhost_records *ref, const char *name, const char *seq, const char *qual, int l, int e,
-                     femgpu_mapping *maps, size_t n, femhost_str *out) {
+                     femgpu_mapping *maps, femgpu_alignment *alns, size_t n, femhost_str *out) {
   if (n == 0) return 0; /* src/map.c:50: unmapped reads print nothing */
   if (g_seq_out['A'] != 'A') init_seq_out();
-  femgpu_sort_mappings(maps, n); /* src/align.c:57 */
+  femgpu_sort_mappings_aln(maps, alns, n); /* src/align.c:57; the device alignments follow their mappings */
   const size_t name_l = strlen(name);
   char rc[l + 1], md[4 * l + 64];
   uint32_t cigar[l + 2];
@@ -217,11 +217,19 @@ int femhost_sam_read(const femhost_records *ref, const char *name, const char *s
       rc[l] = 0;
       have_rc = 1;
     }
-    int n_cigar = 0;
+    int n_cigar = 0, start;
     const char *window = ref->bases + ref->base_off[rec] + cpos;
-    const int start = femhost_alignment(window, m->direction ? rc : seq, l, e, m->edit_distance, m->end_position_offset,
-                                        cigar, &n_cigar, md);
-    if (start == FEMHOST_ALIGN_ERROR) return -2;
+    if (alns && alns[mi].n_cigar != FEMGPU_ALN_HOST) { /* start and CIGAR came from the device (k_trace) */
+      const femgpu_alignment *al = &alns[mi];
+      start = al->start;
+      n_cigar = al->n_cigar;
+      for (int ci = 0; ci < n_cigar; ++ci) cigar[ci] = ((uint32_t)(al->cigar[ci] >> 2) << 4) | (al->cigar[ci] & 3u);
+      md_text(window + start, m->direction ? rc : seq, cigar, n_cigar, md);
+    } else {
+      start = femhost_alignment(window, m->direction ? rc : seq, l, e, m->edit_distance, m->end_position_offset, cigar,
+                                &n_cigar, md);
+      if (start == FEMHOST_ALIGN_ERROR) return -2;
+    }
     const uint32_t pos = (uint32_t)start + cpos; /* src/align.c:80 */
     const char *rname = femhost_record_name(ref, rec);
     const size_t rname_l = strlen(rname), md_l = strlen(md);

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define FEMGPU_ABI_VERSION 1
+#define FEMGPU_ABI_VERSION 2
 
 typedef enum {
   FEMGPU_OK = 0,
@@ -52,6 +52,19 @@ typedef struct {
   uint8_t reserved[2];
 } femgpu_mapping;
 
+/* Start and CIGAR of one mapping as generate_alignment (src/align.c:279-499) produces them,
+ * computed on the device.  40 bytes.  cigar[i] = (length << 2) | op with op 0 M, 1 I, 2 D, in
+ * SAM order.  n_cigar == FEMGPU_ALN_HOST: not computed (a character outside "ACGTN" in the read
+ * or the reference -- the reference compares raw characters there); the host's
+ * femhost_alignment handles those. */
+#define FEMGPU_ALN_HOST 0xFF
+typedef struct {
+  int16_t start;      /* 0-based, relative to candidate_position (src/align.c:78)           */
+  uint8_t n_cigar;
+  uint8_t reserved;
+  uint16_t cigar[18];
+} femgpu_alignment;
+
 /* One batch of reads: what a SequenceBatch (src/sequence_batch.h:15-24) holds, flattened.
  * bases: the reads' sequence characters back to back (any case, non-ACGT = ambiguous);
  * offsets[i]..offsets[i+1] delimit read i.  Host memory, pinned or pageable. */
@@ -81,6 +94,7 @@ typedef struct {
   const uint64_t *first;      /* n_reads + 1 */
   const femgpu_mapping *maps; /* first[n_reads] records */
   femgpu_stats stats;         /* this batch only */
+  const femgpu_alignment *alns; /* parallel to maps; NULL when "device_traceback" is off */
 } femgpu_result;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */
@@ -98,7 +112,8 @@ void femgpu_free_pinned(void *p);
 
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
  * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan),
- * "cand_mode" (0 hash path first, 1 sort path only), "hash_slots" (0 automatic).  Returns FEMGPU_EINVAL for unknown keys. */
+ * "cand_mode" (0 hash path first, 1 sort path only), "hash_slots" (0 automatic),
+ * "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 
 /* ---- resident data --------------------------------------------------------------------------- */
@@ -151,12 +166,14 @@ int femgpu_candidates_batch(femgpu_ctx *ctx, const femgpu_params *params,
 /* src/align.c:53-57 + src/ksort.h:98-151: the reference's per-read mapping order (host side,
  * used by the SAM writer; exported so callers get the same permutation on ties). */
 void femgpu_sort_mappings(femgpu_mapping *maps, size_t n);
+/* the same, carrying the parallel array of device alignments along (alns may be NULL) */
+void femgpu_sort_mappings_aln(femgpu_mapping *maps, femgpu_alignment *alns, size_t n);
 
 /* ---- measurement hooks ------------------------------------------------------------------------ */
 /* Device time (CUDA events on the context's stream) of the kernels of the last finished batch, in
- * milliseconds: [0] pack+seed, [1] candidates, [2] verify, [3] compaction, [4] whole device
- * pipeline including H2D/D2H.  n_launches receives the number of kernel launches. */
-int femgpu_last_timings(femgpu_ctx *ctx, float ms[5], uint32_t *n_launches);
+ * milliseconds: [0] pack+seed, [1] candidates, [2] verify, [3] compaction, [4] traceback,
+ * [5] whole device pipeline including H2D/D2H.  n_launches receives the number of kernel launches. */
+int femgpu_last_timings(femgpu_ctx *ctx, float ms[6], uint32_t *n_launches);
 /* Work counters of the last finished batch, the numerators of the roofline figures: [0] banded
  * Myers columns actually computed by the verification kernel, [1] candidates verified,
  * [2] occurrence-table entries of the selected seeds ("candidates before additional q-gram
@@ -164,7 +181,7 @@ int femgpu_last_timings(femgpu_ctx *ctx, float ms[5], uint32_t *n_launches);
 int femgpu_last_work(femgpu_ctx *ctx, uint64_t work[4]);
 /* Run the device pipeline of the last submitted batch again with inputs already resident in HBM
  * (no H2D, no D2H of mappings); returns device milliseconds.  bench.py's `value`. */
-int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[4]);
+int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[5]);
 
 /* INT32 pipe peak of the device in 10^9 instructions per second, measured with dependency-chain
  * free kernels: [0] LOP3 (logic), [1] IADD3 (add), [2] shift+logic pairs as in the Myers column.

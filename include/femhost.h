@@ -59,6 +59,10 @@ void femhost_reader_close(femhost_reader *rd);
 int64_t femhost_reader_next(femhost_reader *rd, uint32_t max_records, femhost_records *out);
 /* src/sequence_batch.c:82-121 */
 int femhost_load_all(const char *path, femhost_records *out);
+/* The same records for a plain four-line FASTQ file, read the way femhost_map_file's parallel
+ * reader does: independent byte ranges of chunk_bytes that resynchronise on record starts.
+ * Returns 1 (and callers fall back to femhost_load_all) when the file is not of that shape. */
+int femhost_load_all_ranges(const char *path, uint64_t chunk_bytes, femhost_records *out);
 
 /* ---- index ------------------------------------------------------------------------------------ */
 /* src/index.h:7-14 */
@@ -94,10 +98,12 @@ int femhost_sam_header(const femhost_records *ref, femhost_str *out);
 int femhost_alignment(const char *window, const char *text, int l, int e, int edit_distance,
                       int end_offset, uint32_t *cigar, int *n_cigar, char *md);
 /* src/align.c:56-92 + htslib sam.c:3004-3061 for one read: sorts maps[0..n) in place with the
- * reference's own order (src/align.c:57) and appends one SAM line per mapping. */
+ * reference's own order (src/align.c:57) and appends one SAM line per mapping.  alns (may be
+ * NULL) are the device's start/CIGAR per mapping (femgpu_result.alns), permuted along; entries
+ * marked FEMGPU_ALN_HOST and all entries of a NULL array are computed here by femhost_alignment. */
 int femhost_sam_read(const femhost_records *ref, const char *name, const char *seq,
-                     const char *qual, int l, int e, femgpu_mapping *maps, size_t n,
-                     femhost_str *out);
+                     const char *qual, int l, int e, femgpu_mapping *maps, femgpu_alignment *alns,
+                     size_t n, femhost_str *out);
 
 /* ---- the `FEM map` engine ---------------------------------------------------------------------- */
 /* src/FEM_map.c:136-143: reference records + index, resident on n_gpus devices. */

@@ -113,3 +113,36 @@ def test_read_shards_concatenate_to_the_whole(big):
     m.close()
     assert b"".join(parts) == big["want"]
     assert tuple(total) == big["counters"]
+
+
+def test_reader_paths_agree(big):
+    """parallel byte-range reader (default on plain four-line FASTQ), forced sequential reader, and
+    the automatic fall-back for multi-line / gzip input all give the same SAM file."""
+    import gzip as gz
+    d, sam = big["d"], str(big["d"] / "rp.sam")
+    env = dict(os.environ)
+    from fem_b200.host import FEM_BINARY
+
+    def run(fq, extra_env=None):
+        p = subprocess.run([FEM_BINARY, "map", "-e", str(big["e"]), "-a", str(big["a"]), "-t", "6", "--ref", big["fa"],
+                            "--index", big["idx"], "--read1", fq, "-o", sam, "--batch", "700"],
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, env={**env, **(extra_env or {})})
+        assert p.returncode == 0, p.stderr[-2000:]
+        with open(sam, "rb") as f:
+            return f.read()
+
+    assert run(big["fq"], {"FEM_READER": "kseq"}) == big["want"]
+    assert run(big["fq"], {"FEM_DEVICE_TRACEBACK": "0"}) == big["want"]  # every alignment on the host
+    # sequences wrapped over two lines: not four-line FASTQ -> the run restarts with the kseq reader
+    wrapped = str(d / "wrapped.fq")
+    with open(big["fq"], "rb") as f, open(wrapped, "wb") as g:
+        lines = f.read().split(b"\n")
+        for i in range(0, len(lines) - 3, 4):
+            s, q = lines[i + 1], lines[i + 3]
+            h = len(s) // 2 if (i // 4) % 50 == 49 else len(s)
+            g.write(lines[i] + b"\n" + s[:h] + b"\n" + (s[h:] + b"\n" if h < len(s) else b"") + b"+\n" + q + b"\n")
+    assert run(wrapped) == big["want"]
+    zipped = str(d / "reads.fq.gz")
+    with open(big["fq"], "rb") as f, gz.open(zipped, "wb", compresslevel=1) as g:
+        g.write(f.read())
+    assert run(zipped) == big["want"]

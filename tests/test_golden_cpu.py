@@ -194,3 +194,55 @@ def test_no_fallback_without_a_device():
     _, fa, _, _ = gold(TAGS[0])
     with pytest.raises(FemGpuError):
         host.HostMapper(fa, fa, 1)
+
+
+def test_parallel_reader_ranges_equal_sequential(tmp_path):
+    """Byte-range parsing with record resynchronisation (engine.c's parallel reader) must give the
+    sequential reader's records for every chunk size, also when quality lines begin with '@' or
+    '+', and must decline anything that is not plain four-line FASTQ."""
+    import random
+    from fem_b200 import host
+    rng = random.Random(5)
+    p = str(tmp_path / "r.fq")
+    with open(p, "wb") as f:
+        for i in range(3000):
+            l = rng.choice([1, 2, 36, 100, 151])
+            seq = "".join(rng.choice("ACGTN") for _ in range(l))
+            qual = "".join(rng.choice("@+I#>5") for _ in range(l))
+            f.write(("@r%d some comment\n%s\n+%s\n%s\n" % (i, seq, "r%d" % i if i % 7 == 0 else "", qual)).encode())
+    want = host.load_all(p).as_list()
+    assert len(want) == 3000
+    for chunk in (1, 7, 64, 1000, 4096, 100_000, 10_000_000):
+        got = host.load_all_ranges(p, chunk)
+        assert got is not None and got.as_list() == want, chunk
+    for bad in (b"@a\nAC\nGT\n+\nIIII\n@b\nAC\n+\nII\n", b"@a\r\nAC\r\n+\r\nII\r\n" * 50, b">a\nACGT\n>b\nAC\n",
+                b"x\n@a\nAC\n+\nII\n"):
+        q = str(tmp_path / "bad.fq")
+        with open(q, "wb") as f:
+            f.write(bad)
+        assert host.load_all_ranges(q, 16) is None
+
+
+@pytest.mark.parametrize("n", [1, 2, 40, 64, 65, 300, 70_000])
+def test_sort_with_alignments_follows_the_mapping_permutation(n):
+    """femgpu_sort_mappings_aln = femgpu_sort_mappings on the records, alignments carried along;
+    keys tie on purpose (src/ksort.h's in-place radix sort is not stable above 64 records)."""
+    from fem_b200.api import ALIGNMENT_DTYPE, MAPPING_DTYPE, sort_mappings, sort_mappings_aln
+    rng = np.random.default_rng(n)
+    maps = np.zeros(n, dtype=MAPPING_DTYPE)
+    maps["candidate_position"] = rng.integers(0, 50, size=n).astype(np.uint64) + (rng.integers(0, 2, size=n).astype(np.uint64) << np.uint64(32))
+    maps["end_position_offset"] = rng.integers(99, 104, size=n)
+    maps["direction"] = rng.integers(0, 2, size=n)
+    maps["edit_distance"] = rng.integers(0, 4, size=n)
+    alns = np.zeros(n, dtype=ALIGNMENT_DTYPE)
+    alns["start"] = np.arange(n) % 30000
+    alns["cigar"][:, 0] = np.arange(n) % 65521
+    alns["cigar"][:, 1] = np.arange(n) // 65521
+    ident = (alns["cigar"][:, 0].astype(np.int64) + 65521 * alns["cigar"][:, 1].astype(np.int64)).copy()
+    want = sort_mappings(maps.copy())
+    got_maps, got_alns = sort_mappings_aln(maps.copy(), alns.copy())
+    assert np.array_equal(got_maps, want)
+    src = got_alns["cigar"][:, 0].astype(np.int64) + 65521 * got_alns["cigar"][:, 1].astype(np.int64)
+    assert sorted(src.tolist()) == ident.tolist()
+    for f in ("candidate_position", "end_position_offset", "direction", "edit_distance"):
+        assert np.array_equal(maps[f][src], got_maps[f])  # alignment i still belongs to mapping i

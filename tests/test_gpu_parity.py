@@ -153,6 +153,36 @@ def test_mappings_match_oracle(setup):
     assert n_checked > 0
 
 
+def test_device_traceback_matches_oracle(setup):
+    """k_trace: start and CIGAR of every mapping (src/align.c:279-499) against the oracle."""
+    from fem_b200.api import ALN_HOST
+    seqs = [r[1] for r in setup.reads[:400]]
+    first, maps, _ = setup.mapper.map_batch(seqs, setup.e, setup.a)
+    alns = setup.mapper.last_alignments
+    assert alns is not None and len(alns) == len(maps)
+    n_dev = 0
+    for i, seq in enumerate(seqs):
+        canonical = set(seq) <= set(b"ACGTN")
+        for j in range(int(first[i]), int(first[i + 1])):
+            m, al = maps[j], alns[j]
+            text = ol.revcomp(seq) if m["direction"] else seq
+            start, cigar, _ = setup.oracle.alignment(int(m["candidate_position"]), text, int(m["edit_distance"]),
+                                                     int(m["end_position_offset"]))
+            if al["n_cigar"] == ALN_HOST:
+                assert not canonical or setup.tag == "withN", "read %d left to the host without need" % i
+                continue
+            n_dev += 1
+            got = [((int(c) >> 2) << 4) | (int(c) & 3) for c in al["cigar"][:al["n_cigar"]]]
+            assert (int(al["start"]), got) == (start, cigar), "read %d mapping %d" % (i, j)
+    assert n_dev > 0
+    setup.mapper.set_option("device_traceback", 0)
+    try:
+        setup.mapper.map_batch(seqs[:50], setup.e, setup.a)
+        assert setup.mapper.last_alignments is None
+    finally:
+        setup.mapper.set_option("device_traceback", 1)
+
+
 def test_double_buffered_submit_matches_sync(setup):
     seqs = [r[1] for r in setup.reads]
     half = len(seqs) // 2
