@@ -29,8 +29,20 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOAD = dict(name="cfg2: 100 Mbp random reference (10 records), 1M x 100 bp SE reads, e=5, window 12 / step 4",
-                ref_bp=100_000_000, ref_records=10, reads=1_000_000, read_len=100, e=5, a=1, k=12, step=4, seed=2)
+WORKLOADS = {
+    # BASELINE.json configs[0..4]; cfg4 as written is infeasible in the reference and is restated as cfg4p
+    "cfg1": dict(name="cfg1: 4.6 Mbp random reference (4 records), 100k x 100 bp SE reads, e=3, window 12 / step 5",
+                 ref_bp=4_600_000, ref_records=4, repeat_permille=0, reads=100_000, read_len=100, e=3, a=1, k=12, step=5, seed=1),
+    "cfg2": dict(name="cfg2: 100 Mbp random reference (10 records), 1M x 100 bp SE reads, e=5, window 12 / step 4",
+                 ref_bp=100_000_000, ref_records=10, repeat_permille=0, reads=1_000_000, read_len=100, e=5, a=1, k=12, step=4, seed=2),
+    "cfg3": dict(name="cfg3: 3.1 Gbp random reference (24 records), 10M x 150 bp SE reads, e=7, window 12 / step 5",
+                 ref_bp=3_100_000_000, ref_records=24, repeat_permille=0, reads=10_000_000, read_len=150, e=7, a=1, k=12, step=5, seed=3),
+    "cfg4p": dict(name="cfg4': 3.1 Gbp repeat-rich reference (10% repeats, 24 records), 10M x 150 bp SE reads, e=7, window 12 / step 2",
+                  ref_bp=3_100_000_000, ref_records=24, repeat_permille=100, reads=10_000_000, read_len=150, e=7, a=1, k=12, step=2, seed=4),
+    "cfg5": dict(name="cfg5: 3.1 Gbp random reference (24 records), 50M x 250 bp SE reads, e=7, window 14 / step 10",
+                 ref_bp=3_100_000_000, ref_records=24, repeat_permille=0, reads=50_000_000, read_len=250, e=7, a=1, k=14, step=10, seed=5),
+}
+WORKLOAD = dict(WORKLOADS["cfg2"])  # the metric's single-GPU configuration; --workload selects another
 FEMSIM = os.path.join(ROOT, "tools", "femsim")
 REF_HDR = os.path.join(ROOT, "oracle", "_ref", "FEM_ref_hdr")
 
@@ -41,13 +53,19 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--reads", type=int, default=WORKLOAD["reads"], help="reads per GPU (default: the config's 1M)")
-    ap.add_argument("--ref-bp", type=int, default=WORKLOAD["ref_bp"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--reads", type=int, default=0, help="reads per GPU (default: the workload's)")
+    ap.add_argument("--ref-bp", type=int, default=0)
     ap.add_argument("--data-dir", default=os.environ.get("FEM_BENCH_DIR", "/tmp/fem_bench"))
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="reads of the workload the CPU baseline maps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (default: --steps)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    WORKLOAD.clear()
+    WORKLOAD.update(WORKLOADS[args.workload])
+    args.reads = args.reads or WORKLOAD["reads"]
+    args.ref_bp = args.ref_bp or WORKLOAD["ref_bp"]
+    return args
 
 
 def dist_env():
@@ -62,22 +80,22 @@ def ensure_data(args, rank, world, barrier):
     """Synthetic inputs (untimed): reference + index shared by all ranks, one reads file per rank."""
     from fem_b200 import host
     w = WORKLOAD
-    d = os.path.join(args.data_dir, "ref%d_k%d_s%d" % (args.ref_bp, w["k"], w["step"]))
+    d = os.path.join(args.data_dir, "ref%d_rep%d_k%d_s%d" % (args.ref_bp, w["repeat_permille"], w["k"], w["step"]))
     os.makedirs(d, exist_ok=True)
     fa, idx = os.path.join(d, "ref.fa"), os.path.join(d, "index")
     if rank == 0:
         if not os.path.exists(fa + ".ok"):
             t = time.time()
-            subprocess.check_call([FEMSIM, "ref", str(w["seed"]), str(args.ref_bp), str(w["ref_records"]), "0", fa])
+            subprocess.check_call([FEMSIM, "ref", str(w["seed"]), str(args.ref_bp), str(w["ref_records"]), str(w["repeat_permille"]), fa])
             open(fa + ".ok", "w").close()
             log("reference generated in %.1fs" % (time.time() - t))
         if not os.path.exists(idx + ".ok"):
             t = time.time()
-            subprocess.check_call([host.FEM_BINARY, "index", str(w["k"]), str(w["step"]), fa, idx], stderr=subprocess.DEVNULL)
+            subprocess.check_call([host.FEM_BINARY, "index", str(w["k"]), str(w["step"]), fa, idx, "--gpu"], stderr=subprocess.DEVNULL)
             open(idx + ".ok", "w").close()
             log("index built in %.1fs" % (time.time() - t))
     barrier()
-    fq = os.path.join(d, "reads_%d_r%d.fq" % (args.reads, rank))
+    fq = os.path.join(d, "reads_%d_l%d_e%d_r%d.fq" % (args.reads, w["read_len"], w["e"], rank))
     if not os.path.exists(fq + ".ok"):
         subprocess.check_call([FEMSIM, "reads", str(1000 + w["seed"] + rank), fa, str(args.reads), str(w["read_len"]),
                                str(w["e"]), fq])
@@ -164,6 +182,17 @@ def time_reference(fa, idx, fq, e, a, threads, out_sam):
     return secs, reads
 
 
+def sam_groups(path):
+    """SAM records grouped by QNAME in file order (reference -t N interleaves reads but keeps each read's
+    records contiguous and ordered); header lines under the key None."""
+    groups = {}
+    with open(path, "rb") as f:
+        for line in f:
+            key = None if line.startswith(b"@") else line.split(b"\t", 1)[0]
+            groups.setdefault(key, []).append(line)
+    return groups
+
+
 def cpu_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -175,7 +204,7 @@ def config_dict(args, world):
     w = WORKLOAD
     return {"workload": w["name"], "reads_per_gpu": args.reads, "read_len": w["read_len"], "e": w["e"], "a": w["a"],
             "window": w["k"], "step": w["step"], "reference_bp": args.ref_bp, "sharding": "reads sharded per GPU, index replicated, no collective",
-            "l2": "inputs larger than L2 (index %.0f MB + reads, re-streamed every step)" % (67.1 + 8.0 * args.ref_bp / w["step"] / 1e6)}
+            "l2": "inputs larger than L2 (index %.0f MB + reads, re-streamed every step)" % (4.0 * (4 ** w["k"] + 1) / 1e6 + 8.0 * args.ref_bp / w["step"] / 1e6)}
 
 
 def run_reference(args):
@@ -340,7 +369,14 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline and os.access(REF_HDR, os.X_OK):
         sample = head_fastq(fq, fq + ".cpu%d" % args.cpu_sample, args.cpu_sample)
         secs, n = time_reference(fa, idx, sample, w["e"], w["a"], cores, out + ".ref")
+        # untimed: the same sample through this repository's path, compared record for record
+        hm.map_file(sample, out + ".ours", w["e"], w["a"], threads=threads)
+        ref_g, our_g = sam_groups(out + ".ref"), sam_groups(out + ".ours")
+        line["parity_vs_reference"] = {"reads": n, "sam_records": sum(len(v) for k, v in ref_g.items() if k is not None),
+                                       "identical": ref_g == our_g,
+                                       "how": "header + per-read record groups (content and order) of oracle/_ref/FEM_ref_hdr -t %d vs femhost_map_file on the same reads" % cores}
         os.remove(out + ".ref")
+        os.remove(out + ".ours")
         line["cpu_baseline"] = {"value": n / secs, "unit": "reads/s", "cores": cores, "kind": "reference",
                                 "sample": "first %d reads of the workload, oracle/_ref/FEM_ref_hdr map -t %d, its own Time: window" % (n, cores)}
     elif world == 1 and not args.no_cpu_baseline:

@@ -75,6 +75,10 @@ EXPORTS = {
     "femgpu_upload_index": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "femgpu_upload_index_file": (C.c_int, [C.c_void_p, C.c_char_p]),
     "femgpu_upload_reference": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]),
+    "femgpu_build_index": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "femgpu_index_sizes": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "femgpu_download_index": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "femgpu_save_index_file": (C.c_int, [C.c_void_p, C.c_char_p]),
     "femgpu_index_k": (C.c_int, [C.c_void_p]),
     "femgpu_index_step": (C.c_int, [C.c_void_p]),
     "femgpu_map_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Result)]),
@@ -188,6 +192,20 @@ class Mapper:
         occ = np.ascontiguousarray(occ, dtype=np.uint64)
         _check(self.lib.femgpu_upload_index(self.h, k, step, lut.ctypes.data, lut.size,
                                             occ.ctypes.data if occ.size else None, occ.size))
+
+    def build_index(self, k, step):
+        """src/index.c:57-98 construct_index, on the device from the uploaded reference"""
+        _check(self.lib.femgpu_build_index(self.h, k, step))
+
+    def download_index(self):
+        ln, on = C.c_size_t(0), C.c_size_t(0)
+        _check(self.lib.femgpu_index_sizes(self.h, C.byref(ln), C.byref(on)))
+        lut, occ = np.empty(ln.value, dtype=np.uint32), np.empty(on.value, dtype=np.uint64)
+        _check(self.lib.femgpu_download_index(self.h, lut.ctypes.data, lut.size, occ.ctypes.data if occ.size else None, occ.size))
+        return self.lib.femgpu_index_k(self.h), self.lib.femgpu_index_step(self.h), lut, occ
+
+    def save_index(self, path):
+        _check(self.lib.femgpu_save_index_file(self.h, os.fsencode(path)))
 
     def upload_reference(self, records):
         """records: list of (name, bytes)"""

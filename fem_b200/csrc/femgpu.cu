@@ -6,6 +6,7 @@
 #include "../../include/femgpu.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -16,6 +17,8 @@
 #include "common.cuh"
 #include "k_cand.cuh"
 #include "k_cand_hash.cuh"
+#include "k_cand_pair.cuh"
+#include "k_index.cuh"
 #include "k_peak.cuh"
 #include "k_seed.cuh"
 #include "k_trace.cuh"
@@ -148,7 +151,9 @@ struct femgpu_ctx {
   int64_t arena_candidates = 0; // 0 = automatic
   uint32_t sort_capacity = 1024, acc_capacity = 256;
   int l2_persist_lut = 1;
-  int cand_mode = 0;    // 0: hash path first, then sort path, then global scratch; 1: skip the hash path
+  int cand_mode = 0;    // 0: pair path (a >= 1) or hash path (a = 0) first, then sort path, then global scratch;
+                        // 1: sort path only; 2: hash path first; 3: pair path first (a >= 1)
+  uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
   int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan (tests force both)
@@ -220,7 +225,9 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "sort_capacity" && value >= 32 && value <= 8192 && (value & (value - 1)) == 0) c->sort_capacity = (uint32_t)value;
   else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
-  else if (k == "cand_mode" && value >= 0 && value <= 1) c->cand_mode = (int)value;
+  else if (k == "cand_mode" && value >= 0 && value <= 3) c->cand_mode = (int)value;
+  else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 65536 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
+  else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
   else if (k == "device_traceback") c->device_traceback = value != 0;
   else if (k == "seed_dp_mode" && value >= 0 && value <= 2) c->seed_dp_mode = (int)value;
@@ -276,4 +283,5 @@ extern "C" int femgpu_measure_int32_peak(femgpu_ctx *c, double giops[3]) {
 
 #include "upload.inl"
 #include "pipeline.inl"
+#include "index_build.inl"
 #include "api.inl"

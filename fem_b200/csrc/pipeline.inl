@@ -7,6 +7,9 @@ struct Plan { // derived from params + the batch
   size_t cand_smem;   // bytes per block of k_cand
   uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
   size_t hash_smem;
+  uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
+  size_t pair_smem;
+  int first_path; // 0 sort, 1 hash, 2 pair
 };
 
 static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
@@ -44,6 +47,22 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   pl->hash_shift = 64;
   for (uint32_t t = T; t > 1; t >>= 1) --pl->hash_shift;
   pl->hash_smem = 4 * cand_hash_smem_bytes_per_warp(T);
+  // pair path: value buffer for a group's expected location-list total plus six standard deviations,
+  // 32 bitmap bits per expected entry (a few false flags per group)
+  {
+    const double mean = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q;
+    uint32_t VC = c->pair_values;
+    if (!VC) VC = (uint32_t)std::min(2048.0, std::max(64.0, mean + 6.0 * std::sqrt(mean) + 32.0));
+    VC = (VC + 63u) & ~63u;
+    uint32_t M = c->pair_bits;
+    if (!M) M = pow2_ceil_u32((uint32_t)std::min(32768.0, std::max(1024.0, 32.0 * mean)));
+    pl->pair_M = M;
+    pl->pair_VC = VC;
+    pl->pair_shift = 32;
+    for (uint32_t t = M; t > 1; t >>= 1) --pl->pair_shift;
+    pl->pair_smem = 4 * cand_pair_smem_bytes_per_warp(M, VC);
+  }
+  pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
   return 0;
 }
 
@@ -158,6 +177,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
+  if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
 
   Counters hc;
   for (int attempt = 0;; ++attempt) {
@@ -167,13 +187,14 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand_cap = s.cand_cap;
     ca.rs_list = nullptr;
     ca.n_list = 0;
-    if (c->cand_mode == 0) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
+    if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_shift, pl.pair_VC);
+    else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
     else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
     ++s.n_launches;
     CU(cudaGetLastError());
     TRY(read_counters(s, &hc));
     bool arena_full = hc.error_flag == 1;
-    if (c->cand_mode == 0 && !arena_full && hc.overflow_count) {
+    if (pl.first_path != 0 && !arena_full && hc.overflow_count) {
       // ---- sort path for the read-strands the hash path handed on ----------------------------------
       const uint32_t n1 = hc.overflow_count;
       TRY(s.hash_list.reserve((size_t)n1 * 4));

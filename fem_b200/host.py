@@ -59,6 +59,7 @@ EXPORTS = {
     "femhost_load_all": (C.c_int, [C.c_char_p, C.POINTER(RecordsStruct)]),
     "femhost_load_all_ranges": (C.c_int, [C.c_char_p, C.c_uint64, C.POINTER(RecordsStruct)]),
     "femhost_index_build": (C.c_int, [C.POINTER(RecordsStruct), C.c_int, C.c_int, C.POINTER(IndexStruct)]),
+    "femhost_index_build_device": (C.c_int, [C.POINTER(RecordsStruct), C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_double * 3)]),
     "femhost_index_save": (C.c_int, [C.POINTER(IndexStruct), C.c_char_p]),
     "femhost_index_load": (C.c_int, [C.c_char_p, C.POINTER(IndexStruct)]),
     "femhost_index_free": (None, [C.POINTER(IndexStruct)]),
@@ -192,6 +193,14 @@ class Index:
         if ix.lib.femhost_index_build(C.byref(records.c), k, step, C.byref(ix.c)) != 0:
             raise FemGpuError(_err())
         return ix
+
+    @staticmethod
+    def build_on_device(records: Records, k, step, path, device=0):
+        """`FEM index ... --gpu`: the same file from femgpu_build_index; returns (upload, build, save) seconds"""
+        sec = (C.c_double * 3)()
+        if load_host_library().femhost_index_build_device(C.byref(records.c), k, step, device, os.fsencode(path), C.byref(sec)) != 0:
+            raise FemGpuError(_err())
+        return tuple(sec)
 
     @classmethod
     def load(cls, path):

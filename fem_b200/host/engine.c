@@ -124,6 +124,35 @@ fail:
   return NULL;
 }
 
+/* `FEM index` on a GPU: the records go to HBM 2-bit packed, femgpu_build_index produces the arrays of
+ * src/index.c:57-98 there, femgpu_save_index_file streams them into the frozen file layout. */
+int femhost_index_build_device(const femhost_records *ref, int k, int step, int device, const char *out_path,
+                               double seconds[3]) {
+  if (!ref || !out_path || ref->n_records == 0) return femhost_set_error(-1, "index: bad arguments");
+  femgpu_ctx *ctx = femgpu_create(device);
+  if (!ctx) return femhost_set_error(-2, "%s", femgpu_last_error());
+  const char **seqs = (const char **)malloc(ref->n_records * sizeof(char *));
+  uint32_t *lens = (uint32_t *)malloc(ref->n_records * sizeof(uint32_t));
+  for (uint32_t i = 0; i < ref->n_records; ++i) {
+    seqs[i] = ref->bases + ref->base_off[i];
+    lens[i] = femhost_record_length(ref, i);
+  }
+  double t0 = femhost_now();
+  int rc = femgpu_upload_reference(ctx, ref->n_records, seqs, lens);
+  if (seconds) seconds[0] = femhost_now() - t0;
+  t0 = femhost_now();
+  if (!rc) rc = femgpu_build_index(ctx, k, step);
+  if (seconds) seconds[1] = femhost_now() - t0;
+  t0 = femhost_now();
+  if (!rc) rc = femgpu_save_index_file(ctx, out_path);
+  if (seconds) seconds[2] = femhost_now() - t0;
+  if (rc) femhost_set_error(rc, "%s", femgpu_last_error());
+  free(seqs);
+  free(lens);
+  femgpu_destroy(ctx);
+  return rc;
+}
+
 void femhost_mapper_destroy(femhost_mapper *m) {
   if (!m) return;
   pool_free(m);

@@ -2,7 +2,7 @@
  *
  * Same sub-commands, options, output file and statistics lines as the reference's
  * src/FEM.c:23-51, src/FEM_index.c:11-39 and src/FEM_map.c:57-227:
- *   FEM index <window_size> <step_size> <reference> <output>
+ *   FEM index <window_size> <step_size> <reference> <output> [--gpu[=N]]
  *   FEM map -e INT -t INT [-a INT] [-f g] --ref FILE --index FILE --read1 FILE -o FILE
  * Differences, all additive: -t is the number of host threads that build SAM text (the mapping
  * itself runs on the GPUs); --gpus N / FEM_GPUS selects how many devices to use (default 1);
@@ -69,6 +69,16 @@ static int index_main(int argc, char **argv) {
   if (femhost_load_all(argv[3], &ref)) { fprintf(stderr, "%s\n", femhost_last_error()); exit(EXIT_FAILURE); }
   fprintf(stderr, "Number of sequences: %u\nNumber of bases: %" PRIu64 "\nLoaded all sequences successfully in %fs\n",
           ref.n_records, ref.n_bases, real_time() - t0);
+  /* additive: a fifth argument "--gpu[=N]" or FEM_INDEX_GPU=N builds the same file on device N */
+  int device = getenv("FEM_INDEX_GPU") ? atoi(getenv("FEM_INDEX_GPU")) : -1;
+  if (argc > 5 && strncmp(argv[5], "--gpu", 5) == 0) device = argv[5][5] == '=' ? atoi(argv[5] + 6) : 0;
+  if (device >= 0) {
+    double sec[3];
+    if (femhost_index_build_device(&ref, k, step, device, argv[4], sec)) { fprintf(stderr, "%s\n", femhost_last_error()); exit(EXIT_FAILURE); }
+    fprintf(stderr, "Reference resident on GPU %d in %fs.\nBuilt index in %fs.\nSaved index successfully in %fs\n", device, sec[0], sec[1], sec[2]);
+    femhost_records_free(&ref);
+    return 0;
+  }
   t0 = real_time();
   femhost_index idx;
   if (femhost_index_build(&ref, k, step, &idx)) { fprintf(stderr, "%s\n", femhost_last_error()); exit(EXIT_FAILURE); }

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define FEMGPU_ABI_VERSION 2
+#define FEMGPU_ABI_VERSION 3
 
 typedef enum {
   FEMGPU_OK = 0,
@@ -112,7 +112,8 @@ void femgpu_free_pinned(void *p);
 
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
  * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan),
- * "cand_mode" (0 hash path first, 1 sort path only), "hash_slots" (0 automatic),
+ * "cand_mode" (0 automatic: near-pair path when a >= 1, hash path when a = 0; 1 sort path only;
+ * 2 hash path first; 3 near-pair path first), "hash_slots", "pair_bits", "pair_values" (0 automatic),
  * "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 
@@ -130,6 +131,17 @@ int femgpu_upload_index_file(femgpu_ctx *ctx, const char *index_path);
  * raw characters; packed on the device to 2 bits per base plus an ambiguity mask. */
 int femgpu_upload_reference(femgpu_ctx *ctx, uint32_t n_records, const char *const *bases,
                             const uint32_t *lengths);
+/* Stands in for construct_index (src/index.c:57-98) behind `FEM index`: builds the lookup table and
+ * the occurrence table in HBM from the uploaded reference -- the same arrays, entry for entry, as the
+ * reference's two radix sorts produce.  The result is resident exactly as after femgpu_upload_index. */
+int femgpu_build_index(femgpu_ctx *ctx, int32_t k, int32_t step);
+/* Sizes of the resident index: 4^k + 1 lookup-table words, n occurrence words. */
+int femgpu_index_sizes(const femgpu_ctx *ctx, size_t *lookup_table_size, size_t *occurrence_table_size);
+/* The resident arrays back to host memory (sizes must match femgpu_index_sizes). */
+int femgpu_download_index(femgpu_ctx *ctx, uint32_t *lookup_table, size_t lookup_table_size,
+                          uint64_t *occurrence_table, size_t occurrence_table_size);
+/* Stands in for save_index (src/index.c:133-168): the resident index in the frozen file layout. */
+int femgpu_save_index_file(femgpu_ctx *ctx, const char *index_path);
 int femgpu_index_k(const femgpu_ctx *ctx);
 int femgpu_index_step(const femgpu_ctx *ctx);
 

@@ -75,6 +75,10 @@ typedef struct {
 } femhost_index;
 /* src/index.c:57-98 (`FEM index`): same arrays, built by counting sort */
 int femhost_index_build(const femhost_records *ref, int k, int step, femhost_index *out);
+/* the same file written from a GPU (femgpu_build_index + femgpu_save_index_file); seconds (may be
+ * NULL) receives the upload, build and save times */
+int femhost_index_build_device(const femhost_records *ref, int k, int step, int device, const char *out_path,
+                               double seconds[3]);
 /* src/index.c:133-168 and :100-131; the file layout is frozen */
 int femhost_index_save(const femhost_index *idx, const char *path);
 int femhost_index_load(const char *path, femhost_index *out);

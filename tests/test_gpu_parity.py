@@ -88,7 +88,7 @@ def test_candidates_big_path(setup):
     setup.mapper.set_option("sort_capacity", 32)
     setup.mapper.set_option("acc_capacity", 2)
     try:
-        for mode in (1, 0):  # sort path for everything / hash path first
+        for mode in (1, 2, 0):  # sort path for everything / hash path first / automatic (pair path when a >= 1)
             setup.mapper.set_option("cand_mode", mode)
             check_candidates(setup, seqs)
     finally:
@@ -103,10 +103,28 @@ def test_candidates_hash_path_table_sizes(setup, slots):
     to generous; and the sort path alone must agree with it."""
     seqs = [r[1] for r in setup.reads]
     setup.mapper.set_option("hash_slots", slots)
+    setup.mapper.set_option("cand_mode", 2)
     try:
         check_candidates(setup, seqs)
     finally:
         setup.mapper.set_option("hash_slots", 0)
+        setup.mapper.set_option("cand_mode", 0)
+
+
+@pytest.mark.parametrize("bits,values", [(1024, 32), (1024, 2048), (4096, 128), (65536, 512), (0, 0)])
+def test_candidates_pair_path_sizes(setup, bits, values):
+    """k_cand_pair from a crowded bitmap (nearly every entry falsely flagged, most read-strands handed
+    on to the sort path) and a tiny value buffer to generous ones; (0, 0) is the automatic plan."""
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("pair_bits", bits)
+    setup.mapper.set_option("pair_values", values)
+    setup.mapper.set_option("cand_mode", 3)
+    try:
+        check_candidates(setup, seqs)
+    finally:
+        setup.mapper.set_option("pair_bits", 0)
+        setup.mapper.set_option("pair_values", 0)
+        setup.mapper.set_option("cand_mode", 0)
 
 
 def test_candidates_sort_path_only(setup):
