@@ -226,7 +226,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
   else if (k == "cand_mode" && value >= 0 && value <= 3) c->cand_mode = (int)value;
-  else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 65536 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
+  else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 32768 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
   else if (k == "device_traceback") c->device_traceback = value != 0;

@@ -8,12 +8,13 @@
 // as witness, and on a non-repetitive reference those are the handful of entries at the read's true
 // location out of hundreds.  The warp therefore
 //   pass 1  gathers the group's occurrence runs (all loads of a 128-entry chunk in flight together),
-//           keeps the shifted values in shared memory and marks bit hash(x >> 3) of bitmap A
-//           (bitmap B: the bit was already set -- two entries in one 8-wide bucket);
-//   pass 2  flags an entry iff B holds its own bucket or A holds bucket-1 or bucket+1: entries within
-//           e <= 7 of each other sit in the same or in adjacent buckets, so every entry with a
-//           neighbour is flagged; hash collisions only add a few false flags;
-//   exact   counts, among the flagged entries only, the others in [x, x+e] and drops duplicates;
+//           marks the entry's 8-wide bucket in bitmap A (bitmap B: the bit was already set -- two
+//           entries in one bucket) and keeps only the 16-bit bitmap position per entry;
+//   flags   F = B | (A & (A << 1 | A >> 1)), word-wise: entries within e <= 7 of each other sit in
+//           the same or in adjacent buckets, and adjacent buckets are adjacent bits, so every entry
+//           with a neighbour has its bucket in F; aliasing only adds a few false flags;
+//   pass 2  collects the entries whose bucket is in F and loads their values again (cache hits);
+//   exact   counts, among the flagged entries only, those in [x, x+e];
 // and the survivors go through the same greedy cross-group merge as in k_cand_hash.  The last
 // (most frequent) seed's run counts only up to the maximum of the other runs.
 // Read-strands whose group exceeds the value buffer, the flagged list, the survivor list or the
@@ -26,17 +27,21 @@
 #define PAIR_FC 64u // flagged entries per group
 #define PAIR_SC 32u // survivors per group
 #define PAIR_AC 32u // running candidate list
+#define PAIR_DROPPED 0xFFFFu
 
-// M bits of bitmap A (power of two >= 1024), M/4 bits of bitmap B, VC values
+// M bits per bitmap (power of two, 1024..32768), VC entries per group (multiple of 64)
 __host__ __device__ inline size_t cand_pair_smem_bytes_per_warp(uint32_t M, uint32_t VC) {
-  return (size_t)VC * 8 + (PAIR_FC + PAIR_SC + 2 * PAIR_AC) * 8 + M / 8 + M / 32 + 32 * 4;
+  return (size_t)M / 8 * 2 + (PAIR_SC + 2 * PAIR_AC) * 8 + PAIR_FC * 8 + 48 * 4 + (size_t)VC * 2 + PAIR_FC * 2;
 }
 
-__device__ __forceinline__ uint32_t pair_hash_base(uint64_t v) {
-  return (((uint32_t)v >> 3) + (uint32_t)(v >> 32) * 0x9E3779B1u) * 0x85EBCA6Bu;
+// Bitmap position of the 8-wide bucket of shifted location v.  Adjacent buckets of one record map
+// to adjacent positions (mod M), so "bucket and a neighbour bucket both occupied" is a shift-and-AND
+// over bitmap words; the record number only offsets the positions.
+__device__ __forceinline__ uint32_t pair_bucket(uint64_t v, uint32_t mask) {
+  return (((uint32_t)v >> 3) + (uint32_t)(v >> 32) * 0x9E3779B1u) & mask;
 }
 
-__global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint32_t shift, uint32_t VC) {
+__global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint32_t VC) {
   extern __shared__ uint64_t smem_pair[];
   const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
   const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
@@ -46,25 +51,39 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
     return;
   }
   unsigned char *base = reinterpret_cast<unsigned char *>(smem_pair) + (size_t)wib * cand_pair_smem_bytes_per_warp(M, VC);
-  uint64_t *vals = reinterpret_cast<uint64_t *>(base);
-  uint64_t *flist = vals + VC;
-  uint64_t *surv = flist + PAIR_FC;
+  uint32_t *bmA = reinterpret_cast<uint32_t *>(base);         // occupied buckets
+  uint32_t *bmB = bmA + M / 32;                                // buckets with two entries, then the flag map F
+  uint64_t *surv = reinterpret_cast<uint64_t *>(bmB + M / 32);
   uint64_t *acc = surv + PAIR_SC, *acc2 = acc + PAIR_AC;
-  uint32_t *bmA = reinterpret_cast<uint32_t *>(acc2 + PAIR_AC);
-  uint32_t *bmB = bmA + M / 32;
-  uint32_t *s_b = bmB + M / 128, *s_st = s_b + 10, *s_incl = s_st + 10;
+  uint32_t *flo = reinterpret_cast<uint32_t *>(acc2 + PAIR_AC), *fhi = flo + PAIR_FC;
+  uint32_t *s_b = fhi + PAIR_FC, *s_st = s_b + 16, *s_incl = s_st + 16; // 16 slots each; s_incl padded with ~0
+  uint16_t *hst = reinterpret_cast<uint16_t *>(s_incl + 16);            // bitmap position per entry
+  uint16_t *fj = hst + VC;                                              // flat indices of the flagged entries
   const int Q = A.Q;
-  const uint32_t a = (uint32_t)A.a;
+  const uint32_t a = (uint32_t)A.a, e32 = (uint32_t)A.e, mask = M - 1, wmask = M / 32 - 1;
   const uint64_t e = (uint64_t)A.e;
-  const uint32_t K2 = 0x85EBCA6Bu;
   uint32_t na = 0;
   bool overflow = false;
+  if (lane < 16) s_incl[lane] = 0xFFFFFFFFu;
+  // pass 1 decomposition: the Q-1 first runs side by side, lpr lanes each (lane -> run myrun, entry
+  // sub, sub + lpr, ...): every lane keeps its run's begin / length / shift in registers
+  const uint32_t R = (uint32_t)Q - 1u, lpr = R ? 32u / R : 32u;
+  const uint32_t myrun = lane / lpr, sub = lane - myrun * lpr;
+  const bool runner = myrun < R;
+  // seeds of the next group are fetched while the current one is processed
+  uint32_t nb = 0, nfreq = 0, nst = 0;
+  if ((int)lane < Q) {
+    const size_t so = (size_t)rs * A.step * Q;
+    nb = A.seed_begin[so + lane]; nfreq = A.seed_freq[so + lane]; nst = A.seed_start[so + lane];
+  }
 
   for (int g = 0; g < A.step && !overflow; ++g) {
-    const size_t so = ((size_t)rs * A.step + g) * Q;
-    uint32_t b = 0, f = 0, st = 0;
-    if ((int)lane < Q) { b = A.seed_begin[so + lane]; f = A.seed_freq[so + lane]; st = A.seed_start[so + lane]; }
-    uint32_t incl = f;
+    const uint32_t b = nb, f = nfreq, st = nst;
+    if (g + 1 < A.step && (int)lane < Q) {
+      const size_t so = ((size_t)rs * A.step + g + 1) * Q;
+      nb = A.seed_begin[so + lane]; nfreq = A.seed_freq[so + lane]; nst = A.seed_start[so + lane];
+    }
+    uint32_t incl = (int)lane < Q ? f : 0u;
 #pragma unroll
     for (int d = 1; d < 16; d <<= 1) {
       const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
@@ -76,44 +95,44 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
     if (n_tot > VC) { overflow = true; break; }
     __syncwarp();
     if ((int)lane < Q) { s_b[lane] = b; s_st[lane] = st; s_incl[lane] = incl; }
+    if (lane == 0) hst[n_tot] = PAIR_DROPPED; // pass 2 reads entries in pairs
     {
-      uint4 *z = reinterpret_cast<uint4 *>(bmA); // A and B are contiguous: (M/32 + M/128) words
-      for (uint32_t t = lane; t < (M / 32 + M / 128) / 4; t += 32) z[t] = make_uint4(0u, 0u, 0u, 0u);
+      uint4 *z = reinterpret_cast<uint4 *>(bmA); // A and B are contiguous: 2 * M / 32 words
+      for (uint32_t t = lane; t < M / 64; t += 32) z[t] = make_uint4(0u, 0u, 0u, 0u);
     }
     __syncwarp();
-    // ---- pass 1, runs 0..Q-2: one flat index space, four rounds of loads in flight ---------------
+    // ---- pass 1, runs 0..Q-2 side by side, four rounds of loads in flight ---------------------------
+    // run registers of this lane; with lpr a multiple of 4 every lane group reads one aligned 32-byte
+    // sector per round (the first round of a run starts below its begin by begin mod 4 entries)
+    const uint32_t rb = __shfl_sync(0xffffffffu, b, myrun), rf = __shfl_sync(0xffffffffu, f, myrun);
+    const uint32_t rst = __shfl_sync(0xffffffffu, st, myrun), rex = __shfl_sync(0xffffffffu, incl - f, myrun);
+    const uint32_t skew = (lpr & 3u) == 0 ? (rb & 3u) : 0u;
+    uint32_t rounds = runner ? (rf + skew + lpr - 1) / lpr : 0u;
+    rounds = __reduce_max_sync(0xffffffffu, rounds);
     uint64_t mv = 0;
     bool has = false;
-    uint32_t i0 = 0; // run that holds flat index j0 (warp uniform)
-    for (uint32_t j0 = 0; j0 < n_first; j0 += 128) {
-      while (s_incl[i0] <= j0) ++i0;
+    for (uint32_t it0 = 0; it0 < rounds; it0 += 4) {
       uint64_t o[4];
-      uint32_t sti[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const uint32_t j = j0 + 32u * u + lane;
-        o[u] = 0; sti[u] = 1; // (uint32)0 < 1: dropped
-        if (j < n_first) {
-          uint32_t i = i0;
-          while (s_incl[i] <= j) ++i;
-          const uint32_t first = i ? s_incl[i - 1] : 0u;
-          sti[u] = s_st[i];
-          o[u] = A.occ[(uint64_t)s_b[i] + (j - first)];
-        }
+        const uint32_t k = (it0 + u) * lpr + sub - skew; // wraps below zero for the skewed first lanes: k >= rf
+        o[u] = 0;
+        if (runner && k < rf) o[u] = A.occ[(uint64_t)rb + k];
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const uint32_t j = j0 + 32u * u + lane;
-        if (j < n_first) {
-          uint64_t v = FEM_SENTINEL;
-          if ((uint32_t)o[u] >= sti[u]) { // filter.c:89,106
-            v = o[u] - sti[u];
-            const uint32_t h = pair_hash_base(v) >> shift, bit = 1u << (h & 31u);
-            if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 7], 1u << ((h >> 2) & 31u));
-            if (!has || v > mv) mv = v;
+        const uint32_t k = (it0 + u) * lpr + sub - skew;
+        if (runner && k < rf) {
+          uint32_t h = PAIR_DROPPED;
+          if ((uint32_t)o[u] >= rst) { // filter.c:89,106
+            const uint64_t v = o[u] - rst;
+            h = pair_bucket(v, mask);
+            const uint32_t bit = 1u << (h & 31u);
+            if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
+            mv = v; // the run ascends: the last kept entry is this lane's largest
             has = true;
           }
-          vals[j] = v;
+          hst[rex + k] = (uint16_t)h;
         }
       }
     }
@@ -129,77 +148,101 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
         bool beyond = false;
         if (j < fl) {
           const uint64_t o = A.occ[(uint64_t)bl + j];
-          uint64_t v = FEM_SENTINEL;
+          uint32_t h = PAIR_DROPPED;
           if ((uint32_t)o >= stl) {
             if (o - stl <= mv) {
-              v = o - stl;
-              const uint32_t h = pair_hash_base(v) >> shift, bit = 1u << (h & 31u);
-              if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 7], 1u << ((h >> 2) & 31u));
+              h = pair_bucket(o - stl, mask);
+              const uint32_t bit = 1u << (h & 31u);
+              if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
             } else beyond = true;
           }
-          vals[n_first + j] = v;
+          hst[n_first + j] = (uint16_t)h;
         }
         n_all = n_first + min(fl, j0 + 32u);
         if (__any_sync(0xffffffffu, beyond)) break;
       }
     }
     __syncwarp();
-    // ---- pass 2: entries whose own bucket holds two entries or whose neighbour bucket holds one -----
+    // ---- flag map F = B | (A & (A rotated by one bucket either way)), four words per lane and round --
+    for (uint32_t w0 = 4 * lane; w0 < M / 32; w0 += 128) {
+      const uint4 x = *reinterpret_cast<const uint4 *>(bmA + w0);
+      uint4 y = *reinterpret_cast<const uint4 *>(bmB + w0);
+      const uint32_t lft = bmA[(w0 - 1) & wmask], rgt = bmA[(w0 + 4) & wmask];
+      y.x |= x.x & (__funnelshift_l(lft, x.x, 1) | __funnelshift_r(x.x, x.y, 1));
+      y.y |= x.y & (__funnelshift_l(x.x, x.y, 1) | __funnelshift_r(x.y, x.z, 1));
+      y.z |= x.z & (__funnelshift_l(x.y, x.z, 1) | __funnelshift_r(x.z, x.w, 1));
+      y.w |= x.w & (__funnelshift_l(x.z, x.w, 1) | __funnelshift_r(x.w, rgt, 1));
+      *reinterpret_cast<uint4 *>(bmB + w0) = y;
+    }
+    __syncwarp();
+    // ---- pass 2: flat indices of the entries whose bucket is flagged ----------------------------------
     uint32_t nf = 0;
-    for (uint32_t j0 = 0; j0 < n_all; j0 += 32) {
-      const uint32_t j = j0 + lane;
-      const uint64_t v = j < n_all ? vals[j] : FEM_SENTINEL;
-      bool flag = false;
-      if (v != FEM_SENTINEL) {
-        const uint32_t m = pair_hash_base(v);
-        const uint32_t h0 = m >> shift, hm = (m - K2) >> shift, hp = (m + K2) >> shift;
-        flag = (((bmB[h0 >> 7] >> ((h0 >> 2) & 31u)) | (bmA[hm >> 5] >> (hm & 31u)) | (bmA[hp >> 5] >> (hp & 31u))) & 1u) != 0;
+    for (uint32_t j0 = 0; j0 < n_all; j0 += 64) {
+      const uint32_t j = j0 + 2 * lane;
+      const uint32_t hh = j < n_all ? *reinterpret_cast<const uint32_t *>(hst + j) : 0xFFFFFFFFu; // entries j, j + 1
+      const uint32_t h0 = hh & 0xFFFFu, h1 = j + 1 < n_all ? hh >> 16 : PAIR_DROPPED;
+      const bool f0 = h0 != PAIR_DROPPED && ((bmB[h0 >> 5] >> (h0 & 31u)) & 1u);
+      const bool f1 = h1 != PAIR_DROPPED && ((bmB[h1 >> 5] >> (h1 & 31u)) & 1u);
+      const uint32_t bal0 = __ballot_sync(0xffffffffu, f0), bal1 = __ballot_sync(0xffffffffu, f1);
+      if (bal0 | bal1) {
+        const uint32_t i0 = nf + __popc(bal0 & lanemask_lt()), i1 = nf + __popc(bal0) + __popc(bal1 & lanemask_lt());
+        if (f0 && i0 < PAIR_FC) fj[i0] = (uint16_t)j;
+        if (f1 && i1 < PAIR_FC) fj[i1] = (uint16_t)(j + 1);
+        nf += __popc(bal0) + __popc(bal1);
       }
-      const uint32_t bal = __ballot_sync(0xffffffffu, flag);
-      if (flag) {
-        const uint32_t idx = nf + __popc(bal & lanemask_lt());
-        if (idx < PAIR_FC) flist[idx] = v;
-      }
-      nf += __popc(bal);
     }
     if (nf > PAIR_FC) { overflow = true; break; }
     if (nf < a + 1) continue; // a survivor needs a other flagged entries
     __syncwarp();
-    // ---- exact: distinct flagged values with at least a other flagged entries in [x, x+e] -----------
+    // ---- the flagged entries' values again (L1/L2 hits) --------------------------------------------
+    for (uint32_t t = lane; t < nf; t += 32) {
+      const uint32_t j = fj[t];
+      uint32_t i = 0;
+      while (s_incl[i] <= j) ++i;
+      const uint32_t first = i ? s_incl[i - 1] : 0u;
+      const uint64_t v = A.occ[(uint64_t)s_b[i] + (j - first)] - s_st[i];
+      flo[t] = (uint32_t)v;
+      fhi[t] = (uint32_t)(v >> 32);
+    }
+    __syncwarp();
+    // ---- exact: flagged entries with at least a other flagged entries in [x, x+e] ----------------------
     uint32_t ns = 0;
     for (uint32_t t0 = 0; t0 < nf; t0 += 32) {
       const uint32_t idx = t0 + lane;
-      const uint64_t x = idx < nf ? flist[idx] : 0ull;
+      const uint32_t xlo = idx < nf ? flo[idx] : 0u, xhi = idx < nf ? fhi[idx] : 0xFFFFFFFFu;
       uint32_t cnt = 0;
-      bool dup = false;
-      for (uint32_t j = 0; j < nf; ++j) {
-        const uint64_t y = flist[j];
-        if (j != idx) {
-          cnt += (y - x <= e) ? 1u : 0u;
-          dup = dup || (y == x && j < idx);
-        }
-      }
-      const bool keep = idx < nf && cnt >= a && !dup;
+#pragma unroll 4
+      for (uint32_t j = 0; j < nf; ++j) cnt += (flo[j] - xlo <= e32 && fhi[j] == xhi) ? 1u : 0u;
+      const bool keep = idx < nf && cnt >= a + 1; // cnt includes the entry itself
       const uint32_t bal = __ballot_sync(0xffffffffu, keep);
       if (keep) {
         const uint32_t k = ns + __popc(bal & lanemask_lt());
-        if (k < PAIR_SC) surv[k] = x;
+        if (k < PAIR_SC) surv[k] = ((uint64_t)xhi << 32) | xlo;
       }
       ns += __popc(bal);
     }
     if (ns > PAIR_SC) { overflow = true; break; }
     if (ns == 0) continue;
     __syncwarp();
-    // ---- sort the survivors (rank by counting), then the greedy "> last + e" merge with the
-    //      running list (filter.c:45-78), walked by one lane: both lists are a handful long ----
-    uint64_t x = 0;
+    // ---- sort the survivors (stable rank by counting), drop repeated values, then the greedy
+    //      "> last + e" merge with the running list (filter.c:45-78), walked by one lane ----
+    uint64_t x = FEM_SENTINEL;
     uint32_t rank = 0;
     if (lane < ns) {
       x = surv[lane];
-      for (uint32_t j = 0; j < ns; ++j) rank += surv[j] < x; // values are distinct
+      for (uint32_t j = 0; j < ns; ++j) { const uint64_t y = surv[j]; rank += (y < x || (y == x && j < lane)) ? 1u : 0u; }
     }
     __syncwarp();
     if (lane < ns) surv[rank] = x;
+    __syncwarp();
+    {
+      const uint64_t s = lane < ns ? surv[lane] : FEM_SENTINEL;
+      const bool fresh = lane < ns && (lane == 0 || surv[lane - 1] != s);
+      const uint32_t bal = __ballot_sync(0xffffffffu, fresh);
+      __syncwarp();
+      if (fresh) surv[__popc(bal & lanemask_lt())] = s;
+      ns = __popc(bal);
+    }
     __syncwarp();
     uint32_t no = 0;
     if (lane == 0) {

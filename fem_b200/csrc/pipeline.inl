@@ -56,6 +56,7 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     VC = (VC + 63u) & ~63u;
     uint32_t M = c->pair_bits;
     if (!M) M = pow2_ceil_u32((uint32_t)std::min(32768.0, std::max(1024.0, 32.0 * mean)));
+    M = std::min<uint32_t>(M, 32768u); // bitmap positions are kept in 16 bits, 0xFFFF = dropped
     pl->pair_M = M;
     pl->pair_VC = VC;
     pl->pair_shift = 32;
@@ -187,7 +188,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand_cap = s.cand_cap;
     ca.rs_list = nullptr;
     ca.n_list = 0;
-    if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_shift, pl.pair_VC);
+    if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
     else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
     else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
     ++s.n_launches;

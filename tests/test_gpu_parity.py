@@ -111,7 +111,7 @@ def test_candidates_hash_path_table_sizes(setup, slots):
         setup.mapper.set_option("cand_mode", 0)
 
 
-@pytest.mark.parametrize("bits,values", [(1024, 32), (1024, 2048), (4096, 128), (65536, 512), (0, 0)])
+@pytest.mark.parametrize("bits,values", [(1024, 32), (1024, 2048), (4096, 128), (32768, 512), (0, 0)])
 def test_candidates_pair_path_sizes(setup, bits, values):
     """k_cand_pair from a crowded bitmap (nearly every entry falsely flagged, most read-strands handed
     on to the sort path) and a tiny value buffer to generous ones; (0, 0) is the automatic plan."""
