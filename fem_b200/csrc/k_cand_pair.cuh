@@ -55,8 +55,8 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
   uint32_t *bmB = bmA + M / 32;                                // buckets with two entries, then the flag map F
   uint64_t *surv = reinterpret_cast<uint64_t *>(bmB + M / 32);
   uint64_t *acc = surv + PAIR_SC, *acc2 = acc + PAIR_AC;
-  uint32_t *flo = reinterpret_cast<uint32_t *>(acc2 + PAIR_AC), *fhi = flo + PAIR_FC;
-  uint32_t *s_b = fhi + PAIR_FC, *s_st = s_b + 16, *s_incl = s_st + 16; // 16 slots each; s_incl padded with ~0
+  uint64_t *fv = acc2 + PAIR_AC;                               // values of the flagged entries
+  uint32_t *s_b = reinterpret_cast<uint32_t *>(fv + PAIR_FC), *s_st = s_b + 16, *s_incl = s_st + 16; // 16 slots each; s_incl padded with ~0
   uint16_t *hst = reinterpret_cast<uint16_t *>(s_incl + 16);            // bitmap position per entry
   uint16_t *fj = hst + VC;                                              // flat indices of the flagged entries
   const int Q = A.Q;
@@ -95,7 +95,6 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
     if (n_tot > VC) { overflow = true; break; }
     __syncwarp();
     if ((int)lane < Q) { s_b[lane] = b; s_st[lane] = st; s_incl[lane] = incl; }
-    if (lane == 0) hst[n_tot] = PAIR_DROPPED; // pass 2 reads entries in pairs
     {
       uint4 *z = reinterpret_cast<uint4 *>(bmA); // A and B are contiguous: 2 * M / 32 words
       for (uint32_t t = lane; t < M / 64; t += 32) z[t] = make_uint4(0u, 0u, 0u, 0u);
@@ -109,58 +108,74 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
     const uint32_t skew = (lpr & 3u) == 0 ? (rb & 3u) : 0u;
     uint32_t rounds = runner ? (rf + skew + lpr - 1) / lpr : 0u;
     rounds = __reduce_max_sync(0xffffffffu, rounds);
+    // the last run's first 64 entries are requested now, so that they arrive with the other runs'
+    const uint32_t bl = __shfl_sync(0xffffffffu, b, Q - 1), stl = __shfl_sync(0xffffffffu, st, Q - 1), fl = n_tot - n_first;
+    uint64_t ol0 = 0, ol1 = 0;
+    if (lane < fl) ol0 = A.occ[(uint64_t)bl + lane];
+    if (lane + 32u < fl) ol1 = A.occ[(uint64_t)bl + 32u + lane];
     uint64_t mv = 0;
     bool has = false;
-    for (uint32_t it0 = 0; it0 < rounds; it0 += 4) {
-      uint64_t o[4];
+    {
+      const uint64_t *rp = A.occ + rb;      // entry k of this lane's run
+      uint16_t *hp = hst + rex;
+      uint32_t k = sub - skew;              // wraps below zero for the skewed first lanes: k >= rf
+      const uint32_t lpr4 = 4 * lpr;
+      for (uint32_t it0 = 0; it0 < rounds; it0 += 4, k += lpr4) {
+        uint64_t o[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t k = (it0 + u) * lpr + sub - skew; // wraps below zero for the skewed first lanes: k >= rf
-        o[u] = 0;
-        if (runner && k < rf) o[u] = A.occ[(uint64_t)rb + k];
-      }
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t ku = k + u * lpr;
+          o[u] = 0;
+          if (runner && ku < rf) o[u] = rp[ku];
+        }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t k = (it0 + u) * lpr + sub - skew;
-        if (runner && k < rf) {
-          uint32_t h = PAIR_DROPPED;
-          if ((uint32_t)o[u] >= rst) { // filter.c:89,106
-            const uint64_t v = o[u] - rst;
-            h = pair_bucket(v, mask);
-            const uint32_t bit = 1u << (h & 31u);
-            if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
-            mv = v; // the run ascends: the last kept entry is this lane's largest
-            has = true;
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t ku = k + u * lpr;
+          if (runner && ku < rf) {
+            uint32_t h = PAIR_DROPPED;
+            if ((uint32_t)o[u] >= rst) { // filter.c:89,106
+              const uint64_t v = o[u] - rst;
+              h = pair_bucket(v, mask);
+              const uint32_t bit = 1u << (h & 31u);
+              if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
+              mv = v; // the run ascends: the last kept entry is this lane's largest
+              has = true;
+            }
+            hp[ku] = (uint16_t)h;
           }
-          hst[rex + k] = (uint16_t)h;
         }
       }
+    }
+    // the next group's seeds have arrived by now: pull its occurrence runs into L2 (128-byte lines,
+    // lpr lines per run, four of the last run) while this group is finished
+    if (g + 1 < A.step) {
+      const uint32_t pb = __shfl_sync(0xffffffffu, nb, myrun), pf = __shfl_sync(0xffffffffu, nfreq, myrun);
+      const uint32_t lb = __shfl_sync(0xffffffffu, nb, Q - 1), lf = __shfl_sync(0xffffffffu, nfreq, Q - 1);
+      if (runner && 16u * sub < pf + 15u) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.occ + pb + 16u * sub));
+      if (lane < 4 && 16u * lane < lf + 15u) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.occ + lb + 16u * lane));
     }
     const bool any = __any_sync(0xffffffffu, has);
     if (!any) continue; // nothing to merge the last run into
     mv = warp_max_u64(has ? mv : 0ull);
     // ---- pass 1, last run: entries up to that maximum (ascending, so stop at the first larger one) --
     uint32_t n_all = n_first;
-    {
-      const uint32_t bl = s_b[Q - 1], stl = s_st[Q - 1], fl = n_tot - n_first;
-      for (uint32_t j0 = 0; j0 < fl; j0 += 32) {
-        const uint32_t j = j0 + lane;
-        bool beyond = false;
-        if (j < fl) {
-          const uint64_t o = A.occ[(uint64_t)bl + j];
-          uint32_t h = PAIR_DROPPED;
-          if ((uint32_t)o >= stl) {
-            if (o - stl <= mv) {
-              h = pair_bucket(o - stl, mask);
-              const uint32_t bit = 1u << (h & 31u);
-              if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
-            } else beyond = true;
-          }
-          hst[n_first + j] = (uint16_t)h;
+    for (uint32_t j0 = 0; j0 < fl; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      bool beyond = false;
+      if (j < fl) {
+        const uint64_t o = j0 == 0 ? ol0 : j0 == 32 ? ol1 : A.occ[(uint64_t)bl + j];
+        uint32_t h = PAIR_DROPPED;
+        if ((uint32_t)o >= stl) {
+          if (o - stl <= mv) {
+            h = pair_bucket(o - stl, mask);
+            const uint32_t bit = 1u << (h & 31u);
+            if (atomicOr(&bmA[h >> 5], bit) & bit) atomicOr(&bmB[h >> 5], bit);
+          } else beyond = true;
         }
-        n_all = n_first + min(fl, j0 + 32u);
-        if (__any_sync(0xffffffffu, beyond)) break;
+        hst[n_first + j] = (uint16_t)h;
       }
+      n_all = n_first + min(fl, j0 + 32u);
+      if (__any_sync(0xffffffffu, beyond)) break;
     }
     __syncwarp();
     // ---- flag map F = B | (A & (A rotated by one bucket either way)), four words per lane and round --
@@ -175,20 +190,28 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
       *reinterpret_cast<uint4 *>(bmB + w0) = y;
     }
     __syncwarp();
-    // ---- pass 2: flat indices of the entries whose bucket is flagged ----------------------------------
+    // ---- pass 2: flat indices of the entries whose bucket is flagged, four entries per lane and round;
+    //      a lane's count of flagged entries (0..4) is prefix-summed over the warp from three ballots ----
     uint32_t nf = 0;
-    for (uint32_t j0 = 0; j0 < n_all; j0 += 64) {
-      const uint32_t j = j0 + 2 * lane;
-      const uint32_t hh = j < n_all ? *reinterpret_cast<const uint32_t *>(hst + j) : 0xFFFFFFFFu; // entries j, j + 1
-      const uint32_t h0 = hh & 0xFFFFu, h1 = j + 1 < n_all ? hh >> 16 : PAIR_DROPPED;
-      const bool f0 = h0 != PAIR_DROPPED && ((bmB[h0 >> 5] >> (h0 & 31u)) & 1u);
-      const bool f1 = h1 != PAIR_DROPPED && ((bmB[h1 >> 5] >> (h1 & 31u)) & 1u);
-      const uint32_t bal0 = __ballot_sync(0xffffffffu, f0), bal1 = __ballot_sync(0xffffffffu, f1);
-      if (bal0 | bal1) {
-        const uint32_t i0 = nf + __popc(bal0 & lanemask_lt()), i1 = nf + __popc(bal0) + __popc(bal1 & lanemask_lt());
-        if (f0 && i0 < PAIR_FC) fj[i0] = (uint16_t)j;
-        if (f1 && i1 < PAIR_FC) fj[i1] = (uint16_t)(j + 1);
-        nf += __popc(bal0) + __popc(bal1);
+    for (uint32_t j0 = 0; j0 < n_all; j0 += 128) {
+      const uint32_t j = j0 + 4 * lane;
+      uint32_t fl4 = 0; // bit u: entry j + u is flagged
+      if (j < n_all) {
+        const uint2 hh = *reinterpret_cast<const uint2 *>(hst + j); // entries j .. j + 3
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t h = ((u < 2 ? hh.x : hh.y) >> (16 * (u & 1))) & 0xFFFFu;
+          if (j + u < n_all && h != PAIR_DROPPED) fl4 |= ((bmB[h >> 5] >> (h & 31u)) & 1u) << u;
+        }
+      }
+      const uint32_t any4 = __ballot_sync(0xffffffffu, fl4 != 0);
+      if (any4) {
+        const uint32_t c = __popc(fl4), lt = lanemask_lt();
+        const uint32_t c0 = __ballot_sync(0xffffffffu, c & 1u), c1 = __ballot_sync(0xffffffffu, c & 2u), c2 = __ballot_sync(0xffffffffu, c & 4u);
+        uint32_t idx = nf + __popc(c0 & lt) + 2 * __popc(c1 & lt) + 4 * __popc(c2 & lt);
+        for (uint32_t m = fl4; m; m &= m - 1, ++idx)
+          if (idx < PAIR_FC) fj[idx] = (uint16_t)(j + __ffs(m) - 1);
+        nf += __popc(c0) + 2 * __popc(c1) + 4 * __popc(c2);
       }
     }
     if (nf > PAIR_FC) { overflow = true; break; }
@@ -201,18 +224,21 @@ __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint3
       while (s_incl[i] <= j) ++i;
       const uint32_t first = i ? s_incl[i - 1] : 0u;
       const uint64_t v = A.occ[(uint64_t)s_b[i] + (j - first)] - s_st[i];
-      flo[t] = (uint32_t)v;
-      fhi[t] = (uint32_t)(v >> 32);
+      fv[t] = v;
     }
     __syncwarp();
     // ---- exact: flagged entries with at least a other flagged entries in [x, x+e] ----------------------
     uint32_t ns = 0;
     for (uint32_t t0 = 0; t0 < nf; t0 += 32) {
       const uint32_t idx = t0 + lane;
-      const uint32_t xlo = idx < nf ? flo[idx] : 0u, xhi = idx < nf ? fhi[idx] : 0xFFFFFFFFu;
+      const uint64_t xv = idx < nf ? fv[idx] : FEM_SENTINEL;
+      const uint32_t xlo = (uint32_t)xv, xhi = (uint32_t)(xv >> 32);
       uint32_t cnt = 0;
 #pragma unroll 4
-      for (uint32_t j = 0; j < nf; ++j) cnt += (flo[j] - xlo <= e32 && fhi[j] == xhi) ? 1u : 0u;
+      for (uint32_t j = 0; j < nf; ++j) {
+        const uint64_t y = fv[j];
+        cnt += ((uint32_t)y - xlo <= e32 && (uint32_t)(y >> 32) == xhi) ? 1u : 0u;
+      }
       const bool keep = idx < nf && cnt >= a + 1; // cnt includes the entry itself
       const uint32_t bal = __ballot_sync(0xffffffffu, keep);
       if (keep) {
