@@ -251,6 +251,10 @@ def load_peaks():
 def run_ours(args):
     import ctypes as C
     rank, local_rank, world = dist_env()
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import torch
     torch.cuda.set_device(local_rank)
     dist = None
@@ -343,8 +347,18 @@ def run_ours(args):
                for i, n in enumerate(names)}
     top = max(range(5), key=lambda i: per[i])
     ach = kernels[names[top]]["gbs"]
+    traffic, traffic_src = None, None
+    try:  # DRAM bytes of that kernel per launch, from the committed ncu --set full capture of this workload
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            cap = json.load(f).get(args.workload)
+        if cap and names[top] in cap:
+            traffic = cap[names[top]] / cap["reads"] * n_reads
+            traffic_src = cap["source"] + (" (scaled from %d to %d reads)" % (cap["reads"], n_reads) if cap["reads"] != n_reads else "")
+    except (OSError, ValueError):
+        pass
     roofline = {"kernel": names[top], "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "share_of_step": per[top] / sum(per)}
+                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": algo[names[top]],
+                "peak_source": peak_src, "share_of_step": per[top] / sum(per)}
     giops = (C.c_double * 3)()
     _check(lib.femgpu_measure_int32_peak(ctx, C.byref(giops)))
     int_ops = 24.0 * cols + 12.0 * w["e"] * n_cand  # 24 integer ops per executed column
@@ -383,7 +397,8 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": None, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": "oracle/_ref/FEM_ref_hdr not built"}
     hm.close()
     if rank == 0:
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.destroy_process_group()
     return 0
