@@ -18,6 +18,7 @@
 #include "k_cand.cuh"
 #include "k_cand_hash.cuh"
 #include "k_cand_pair.cuh"
+#include "k_cand_small.cuh"
 #include "k_index.cuh"
 #include "k_peak.cuh"
 #include "k_seed.cuh"
@@ -152,7 +153,7 @@ struct femgpu_ctx {
   uint32_t sort_capacity = 1024, acc_capacity = 256;
   int l2_persist_lut = 1;
   int cand_mode = 0;    // 0: pair path (a >= 1) or hash path (a = 0) first, then sort path, then global scratch;
-                        // 1: sort path only; 2: hash path first; 3: pair path first (a >= 1)
+                        // 1: sort path only; 2: hash path first; 3: pair path first (a >= 1); 4: small path first
   uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
@@ -225,7 +226,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "sort_capacity" && value >= 32 && value <= 8192 && (value & (value - 1)) == 0) c->sort_capacity = (uint32_t)value;
   else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
-  else if (k == "cand_mode" && value >= 0 && value <= 3) c->cand_mode = (int)value;
+  else if (k == "cand_mode" && value >= 0 && value <= 4) c->cand_mode = (int)value;
   else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 32768 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;

@@ -9,7 +9,8 @@ struct Plan { // derived from params + the batch
   size_t hash_smem;
   uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
   size_t pair_smem;
-  int first_path; // 0 sort, 1 hash, 2 pair
+  int first_path; // 0 sort, 1 hash, 2 pair, 3 small
+  size_t small_smem;
 };
 
 static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
@@ -64,6 +65,14 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     pl->pair_smem = 4 * cand_pair_smem_bytes_per_warp(M, VC);
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
+  pl->small_smem = 4 * ((cand_small_smem_bytes_per_warp() + 15) & ~(size_t)15);
+  {
+    // sparse index: all groups of a read-strand at once when their lists are expected to hold < 100 entries
+    const double per_rs = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q * pl->step;
+    const bool fits = (uint32_t)(pl->Q * pl->step) <= SMALL_SEEDS && pl->step <= 64;
+    if (c->cand_mode == 4 || (c->cand_mode == 0 && fits && per_rs <= 100.0)) pl->first_path = 3;
+    if (c->cand_mode == 3 && pl->a < 1) pl->first_path = 1;
+  }
   return 0;
 }
 
@@ -178,6 +187,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
+  if (pl.small_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.small_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
 
   Counters hc;
@@ -188,7 +198,8 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand_cap = s.cand_cap;
     ca.rs_list = nullptr;
     ca.n_list = 0;
-    if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
+    if (pl.first_path == 3) k_cand_small<<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca);
+    else if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
     else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
     else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
     ++s.n_launches;

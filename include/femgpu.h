@@ -113,7 +113,8 @@ void femgpu_free_pinned(void *p);
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
  * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan),
  * "cand_mode" (0 automatic: near-pair path when a >= 1, hash path when a = 0; 1 sort path only;
- * 2 hash path first; 3 near-pair path first), "hash_slots", "pair_bits", "pair_values" (0 automatic),
+ * 2 hash path first; 3 near-pair path first; 4 all-groups-at-once path first, the automatic
+ * choice on sparse indexes), "hash_slots", "pair_bits", "pair_values" (0 automatic),
  * "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 

@@ -88,7 +88,7 @@ def test_candidates_big_path(setup):
     setup.mapper.set_option("sort_capacity", 32)
     setup.mapper.set_option("acc_capacity", 2)
     try:
-        for mode in (1, 2, 0):  # sort path for everything / hash path first / automatic (pair path when a >= 1)
+        for mode in (1, 2, 3, 4, 0):  # sort path for everything / hash path first / automatic (pair path when a >= 1)
             setup.mapper.set_option("cand_mode", mode)
             check_candidates(setup, seqs)
     finally:
@@ -124,6 +124,17 @@ def test_candidates_pair_path_sizes(setup, bits, values):
     finally:
         setup.mapper.set_option("pair_bits", 0)
         setup.mapper.set_option("pair_values", 0)
+        setup.mapper.set_option("cand_mode", 0)
+
+
+def test_candidates_small_path(setup):
+    """k_cand_small (all groups of a read-strand at once) forced on every case: dense cases hand most
+    read-strands on to the sort path, sparse ones stay."""
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("cand_mode", 4)
+    try:
+        check_candidates(setup, seqs)
+    finally:
         setup.mapper.set_option("cand_mode", 0)
 
 
