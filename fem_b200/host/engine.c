@@ -13,7 +13,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
+#include <sys/vfs.h>
 #include <unistd.h>
 
 #include "femhost.h"
@@ -188,6 +190,9 @@ struct batch {
   size_t cap_chunks;
   int chunks_left;          /* guarded by run->mu */
   int writes_left;          /* guarded by run->mu */
+  char *map_base;           /* the batch's span of the output file, mapped (NULL: pwrite) */
+  size_t map_len;
+  uint64_t map_file_off;    /* file offset of map_base[0] */
 };
 
 static void pool_free(femhost_mapper *m) {
@@ -213,6 +218,9 @@ typedef struct {
   int out_fd;               /* -1: build the text, write nothing */
   int out_seekable;         /* regular file: chunks are written in parallel with pwrite */
   uint64_t out_off;         /* next file offset (writer thread only) */
+  int out_populate;         /* madvise(MADV_POPULATE_WRITE) before the copy (FEM_SAM_POPULATE=0 turns it off) */
+  int out_mmap;             /* tmpfs: chunks are copied into a shared mapping (pwrite holds the inode lock) */
+  uint64_t out_alloc;       /* size the file has been extended to (writer thread only) */
   int writes_outstanding;   /* guarded by mu; writer waits for 0 before the file is closed */
   pthread_cond_t writes_done;
   fifo q_free, q_parsed, q_work;
@@ -442,10 +450,24 @@ static void *worker_main(void *arg) {
     batch *b = it->b;
     femhost_str *out = &b->text[it->chunk];
     if (it->write) { /* the writer thread fixed the offset; the copy into the page cache happens here */
-      if (write_all(r->out_fd, out->s, out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
-      wa->busy_write += femhost_now() - t0;
+      if (b->map_base) {
+        char *dst = b->map_base + (it->file_off - b->map_file_off);
+#ifndef MADV_POPULATE_WRITE
+#define MADV_POPULATE_WRITE 23
+#endif
+        if (r->out_populate && out->l) { /* all pages of the chunk in one call instead of one fault each */
+          const uintptr_t pg = (uintptr_t)sysconf(_SC_PAGESIZE), p0 = (uintptr_t)dst & ~(pg - 1);
+          madvise((void *)p0, (size_t)((uintptr_t)dst + out->l - p0), MADV_POPULATE_WRITE);
+        }
+        memcpy(dst, out->s, out->l);
+      }
+      else if (write_all(r->out_fd, out->s, out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
       pthread_mutex_lock(&r->mu);
       const int left = --b->writes_left;
+      pthread_mutex_unlock(&r->mu);
+      if (left == 0 && b->map_base) { munmap(b->map_base, b->map_len); b->map_base = NULL; }
+      wa->busy_write += femhost_now() - t0;
+      pthread_mutex_lock(&r->mu);
       if (--r->writes_outstanding == 0) pthread_cond_broadcast(&r->writes_done);
       pthread_mutex_unlock(&r->mu);
       if (left == 0) fifo_push(&r->q_free, b);
@@ -501,6 +523,23 @@ static void *writer_main(void *arg) {
       r->out_off += len;
       ++n_writes;
     }
+    b->map_base = NULL;
+    if (n_writes && r->out_mmap) { /* extend the file in big steps and map this batch's span of it */
+      const uint64_t hi = r->out_off;
+      uint64_t first = hi;
+      for (uint32_t c = 0; c < b->n_chunks; ++c) if (b->items[c].write && b->items[c].file_off < first) first = b->items[c].file_off;
+      if (hi > r->out_alloc) {
+        const uint64_t want = hi + (256ull << 20);
+        struct statfs fs;
+        if (fstatfs(r->out_fd, &fs) == 0 && (uint64_t)fs.f_bavail * (uint64_t)fs.f_bsize > (want - r->out_alloc) + (64ull << 20) &&
+            ftruncate(r->out_fd, (off_t)want) == 0) r->out_alloc = want;
+      }
+      if (hi <= r->out_alloc) {
+        const uint64_t page = (uint64_t)sysconf(_SC_PAGESIZE), m0 = first & ~(page - 1);
+        void *mp = mmap(NULL, (size_t)(hi - m0), PROT_READ | PROT_WRITE, MAP_SHARED, r->out_fd, (off_t)m0);
+        if (mp != MAP_FAILED) { b->map_base = (char *)mp; b->map_len = (size_t)(hi - m0); b->map_file_off = m0; }
+      }
+    }
     if (n_writes) { /* hand the copies to the workers; the last one recycles the batch */
       pthread_mutex_lock(&r->mu);
       b->writes_left = n_writes;
@@ -526,6 +565,7 @@ static void *writer_main(void *arg) {
   pthread_mutex_lock(&r->mu);
   while (r->writes_outstanding) pthread_cond_wait(&r->writes_done, &r->mu);
   pthread_mutex_unlock(&r->mu);
+  if (r->out_alloc && ftruncate(r->out_fd, (off_t)r->out_off) != 0) run_fail(r, "truncating the SAM file to its size failed");
   r->tm.write = busy;
   return NULL;
 }
@@ -569,7 +609,7 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   }
   r.out_fd = -1;
   if (sam_path) {
-    r.out_fd = open(sam_path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    r.out_fd = open(sam_path, O_RDWR | O_CREAT | O_TRUNC, 0644);
     if (r.out_fd < 0) {
       if (r.rd) femhost_reader_close(r.rd);
       if (r.fd >= 0) close(r.fd);
@@ -577,6 +617,12 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     }
     struct stat ost;
     r.out_seekable = fstat(r.out_fd, &ost) == 0 && S_ISREG(ost.st_mode);
+    /* FEM_SAM_MMAP=1/0 forces the mapped / the pwrite form; default: mapped on tmpfs, where every
+     * pwrite to one file serialises on the inode lock while page faults of a shared mapping do not */
+    struct statfs fs;
+    const char *mm = getenv("FEM_SAM_MMAP");
+    r.out_populate = !(getenv("FEM_SAM_POPULATE") && atoi(getenv("FEM_SAM_POPULATE")) == 0);
+    r.out_mmap = r.out_seekable && (mm ? atoi(mm) != 0 : (fstatfs(r.out_fd, &fs) == 0 && fs.f_type == 0x01021994));
   }
   pthread_cond_init(&r.writes_done, NULL);
   const double t_start = femhost_now();

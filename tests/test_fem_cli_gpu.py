@@ -132,6 +132,18 @@ def test_reader_paths_agree(big):
             return f.read()
 
     assert run(big["fq"], {"FEM_READER": "kseq"}) == big["want"]
+    # the two ways the chunks reach the file: copies into a shared mapping / positional writes
+    assert run(big["fq"], {"FEM_SAM_MMAP": "1"}) == big["want"]
+    assert run(big["fq"], {"FEM_SAM_MMAP": "0"}) == big["want"]
+    if os.path.isdir("/dev/shm"):  # tmpfs picks the mapped form by itself
+        shm = "/dev/shm/fem_test_%d.sam" % os.getpid()
+        try:
+            run_fem_map(big["fa"], big["idx"], big["fq"], shm, big["e"], big["a"], threads=5, extra=("--batch", "900"))
+            with open(shm, "rb") as f:
+                assert f.read() == big["want"]
+        finally:
+            if os.path.exists(shm):
+                os.remove(shm)
     assert run(big["fq"], {"FEM_DEVICE_TRACEBACK": "0"}) == big["want"]  # every alignment on the host
     # sequences wrapped over two lines: not four-line FASTQ -> the run restarts with the kseq reader
     wrapped = str(d / "wrapped.fq")
