@@ -47,11 +47,11 @@ class Stats(C.Structure):
 
 
 class AlignmentRec(C.Structure):
-    _fields_ = [("start", C.c_int16), ("n_cigar", C.c_uint8), ("reserved", C.c_uint8), ("cigar", C.c_uint16 * 18)]
+    _fields_ = [("start", C.c_int16), ("n_cigar", C.c_uint8), ("md_len", C.c_uint8), ("cigar", C.c_uint16 * 18), ("md", C.c_char * 48)]
 
 
-ALIGNMENT_DTYPE = np.dtype([("start", "<i2"), ("n_cigar", "u1"), ("reserved", "u1"), ("cigar", "<u2", (18,))])
-assert ALIGNMENT_DTYPE.itemsize == 40 == C.sizeof(AlignmentRec)
+ALIGNMENT_DTYPE = np.dtype([("start", "<i2"), ("n_cigar", "u1"), ("md_len", "u1"), ("cigar", "<u2", (18,)), ("md", "S48")])
+assert ALIGNMENT_DTYPE.itemsize == 88 == C.sizeof(AlignmentRec)
 ALN_HOST = 0xFF
 
 
@@ -228,7 +228,7 @@ class Mapper:
         else:
             maps = np.zeros(0, dtype=MAPPING_DTYPE)
         # device start/CIGAR per mapping (k_trace), parallel to maps; None when switched off
-        self.last_alignments = (np.frombuffer(C.string_at(res.alns, n * 40), dtype=ALIGNMENT_DTYPE).copy()
+        self.last_alignments = (np.frombuffer(C.string_at(res.alns, n * 88), dtype=ALIGNMENT_DTYPE).copy()
                                 if n and res.alns else None)
         return first, maps, res.stats.as_tuple()
 

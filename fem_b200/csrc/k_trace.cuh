@@ -4,8 +4,8 @@
 // The reference recomputes the band in 32-bit words keeping D0 and HP of every column
 // (src/align.c:303-338), then walks back from the end cell consuming exactly `edit_distance`
 // errors (:340-440) and emits the run-length operations reversed (:441-498).  The same walk is
-// done here per thread with the two per-column words in local memory; the host (sam.c) keeps only
-// the MD string and the text formatting.  The reference compares RAW characters in this function
+// done here per thread with the two per-column words in local memory, followed by the MD text of
+// src/align.c:501-544 (generate_MD_tag); the host (sam.c) keeps only the text formatting.  The reference compares RAW characters in this function
 // while the band uses base codes; codes and characters agree exactly when every
 // character is one of "ACGTN", so mappings of reads (or references) with any other character are
 // flagged FEMGPU_ALN_HOST and the host runs its own femhost_alignment on them.
@@ -26,7 +26,7 @@ struct TraceArgs {
   uint64_t n_maps;
   int e;
   int ref_canonical;
-  uint32_t *aln;               // out: 10 words per mapping (femgpu_alignment, 40 bytes)
+  uint32_t *aln;               // out: 22 words per mapping (femgpu_alignment, 88 bytes)
 };
 
 template <bool HAS_N>
@@ -36,17 +36,70 @@ __device__ __forceinline__ uint32_t ref_code_fetch(const DevRef &R, uint64_t g) 
   return c;
 }
 
-__device__ __forceinline__ void aln_store(uint32_t *dst, int start, uint32_t n_cigar, const uint16_t *cig) {
-  dst[0] = ((uint32_t)(uint16_t)(int16_t)start) | (n_cigar << 16);
+#define ALN_WORDS 22
+#define ALN_MD_MAX 47
+
+__device__ __forceinline__ void aln_store(uint32_t *dst, int start, uint32_t n_cigar, const uint16_t *cig, uint32_t md_len = ALN_HOST) {
+  dst[0] = ((uint32_t)(uint16_t)(int16_t)start) | (n_cigar << 16) | (md_len << 24);
 #pragma unroll
   for (int i = 0; i < ALN_MAX_OPS / 2; ++i) dst[1 + i] = (uint32_t)cig[2 * i] | ((uint32_t)cig[2 * i + 1] << 16);
+}
+
+// decimal digits of v appended at md[o..]; returns the new length (may exceed ALN_MD_MAX: caller checks)
+__device__ __forceinline__ int md_put_uint(char *md, int o, uint32_t v) {
+  char tmp[10];
+  int n = 0;
+  do { tmp[n++] = (char)('0' + v % 10u); v /= 10u; } while (v);
+  while (n) { if (o < 48) md[o] = tmp[n - 1]; ++o; --n; }
+  return o;
+}
+
+// generate_MD_tag (src/align.c:501-544) for a CIGAR in femgpu_alignment encoding; the reference starts at
+// gref, the read codes at text.  Characters are those of a canonical ("ACGTN") reference.  Writes the
+// twelve MD words of the record and returns the length, or ALN_HOST when the text does not fit.
+template <bool HAS_N>
+__device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t *text, const uint16_t *cig, int nc, uint32_t *dst) {
+  char md[48];
+  int o = 0, tp = 0;
+  uint32_t run = 0;
+  for (int ci = 0; ci < nc; ++ci) {
+    const uint32_t op = cig[ci] & 3u, len = cig[ci] >> 2;
+    if (op == 0) {
+      for (uint32_t j = 0; j < len; ++j, ++gref, ++tp) {
+        const uint32_t c = ref_code_fetch<HAS_N>(R, gref);
+        if (c == text[tp]) { ++run; continue; }
+        if (run) { o = md_put_uint(md, o, run); run = 0; }
+        if (o < 48) md[o] = "ACGTN"[c];
+        ++o;
+      }
+    } else if (op == 1) {
+      tp += (int)len;
+    } else {
+      if (run) { o = md_put_uint(md, o, run); run = 0; }
+      if (o < 48) md[o] = '^';
+      ++o;
+      for (uint32_t j = 0; j < len; ++j, ++gref) {
+        if (o < 48) md[o] = "ACGTN"[ref_code_fetch<HAS_N>(R, gref)];
+        ++o;
+      }
+    }
+    if (o > ALN_MD_MAX) return ALN_HOST;
+  }
+  if (run) o = md_put_uint(md, o, run);
+  if (o > ALN_MD_MAX) return ALN_HOST;
+  for (int i = o; i < 48; ++i) md[i] = 0;
+#pragma unroll
+  for (int w = 0; w < 12; ++w)
+    dst[w] = (uint32_t)(uint8_t)md[4 * w] | ((uint32_t)(uint8_t)md[4 * w + 1] << 8) | ((uint32_t)(uint8_t)md[4 * w + 2] << 16) |
+             ((uint32_t)(uint8_t)md[4 * w + 3] << 24);
+  return (uint32_t)o;
 }
 
 template <bool HAS_N, int LCAP>
 __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   const uint64_t mi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (mi >= A.n_maps) return;
-  uint32_t *out = A.aln + mi * 10;
+  uint32_t *out = A.aln + mi * ALN_WORDS;
   uint16_t cig[ALN_MAX_OPS];
 #pragma unroll
   for (int i = 0; i < ALN_MAX_OPS; ++i) cig[i] = 0;
@@ -70,7 +123,14 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   }
   if (diff == 0) {
     cig[0] = (uint16_t)(l << 2);
-    aln_store(out, start, 1, cig);
+    char md[48]; // no difference: the MD text is the read length
+    const int o = md_put_uint(md, 0, (uint32_t)l);
+    for (int i = o; i < 48; ++i) md[i] = 0;
+#pragma unroll
+    for (int w = 0; w < 12; ++w)
+      out[10 + w] = (uint32_t)(uint8_t)md[4 * w] | ((uint32_t)(uint8_t)md[4 * w + 1] << 8) | ((uint32_t)(uint8_t)md[4 * w + 2] << 16) |
+                    ((uint32_t)(uint8_t)md[4 * w + 3] << 24);
+    aln_store(out, start, 1, cig, (uint32_t)o);
     return;
   }
   // :303-338 the band again, 32-bit words, D0 and HP of every column kept
@@ -146,5 +206,5 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   if (fail || n_ops - first + 1 > ALN_MAX_OPS) { aln_store(out, 0, ALN_HOST, cig); return; }
   int nc = 0;
   for (int i = n_ops; i >= first; --i) cig[nc++] = (uint16_t)(((uint32_t)cnt[i] << 2) | ops[i]);
-  aln_store(out, start, (uint32_t)nc, cig);
+  aln_store(out, start, (uint32_t)nc, cig, md_build_store<HAS_N>(A.ref, g0 + (uint64_t)start, text, cig, nc, out + 10));
 }

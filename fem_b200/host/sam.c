@@ -198,6 +198,13 @@ static void init_seq_out(void) {
   memcpy(g_seq_out, t, sizeof t);
 }
 
+/* src/sequence_batch.h:90-98 */
+static void make_rc(const char *seq, int l, char *rc) {
+  static const char back[8] = {'A', 'C', 'G', 'T', 'N', 'N', 'N', 'N'};
+  for (int i = 0; i < l; ++i) rc[i] = back[3 ^ FEM_CODE(seq[l - 1 - i])];
+  rc[l] = 0;
+}
+
 int femhost_sam_read(const femhost_records *ref, const char *name, const char *seq, const char *qual, int l, int e,
                      femgpu_mapping *maps, femgpu_alignment *alns, size_t n, femhost_str *out) {
   if (n == 0) return 0; /* src/map.c:50: unmapped reads print nothing */
@@ -211,12 +218,6 @@ int femhost_sam_read(const femhost_records *ref, const char *name, const char *s
     const femgpu_mapping *m = &maps[mi];
     const uint32_t rec = (uint32_t)(m->candidate_position >> 32), cpos = (uint32_t)m->candidate_position;
     if (rec >= ref->n_records) return femhost_set_error(-1, "mapping names record %u of %u", rec, ref->n_records);
-    if (m->direction && !have_rc) { /* src/sequence_batch.h:90-98 */
-      static const char back[8] = {'A', 'C', 'G', 'T', 'N', 'N', 'N', 'N'};
-      for (int i = 0; i < l; ++i) rc[i] = back[3 ^ FEM_CODE(seq[l - 1 - i])];
-      rc[l] = 0;
-      have_rc = 1;
-    }
     int n_cigar = 0, start;
     const char *window = ref->bases + ref->base_off[rec] + cpos;
     if (alns && alns[mi].n_cigar != FEMGPU_ALN_HOST) { /* start and CIGAR came from the device (k_trace) */
@@ -224,8 +225,15 @@ int femhost_sam_read(const femhost_records *ref, const char *name, const char *s
       start = al->start;
       n_cigar = al->n_cigar;
       for (int ci = 0; ci < n_cigar; ++ci) cigar[ci] = ((uint32_t)(al->cigar[ci] >> 2) << 4) | (al->cigar[ci] & 3u);
-      md_text(window + start, m->direction ? rc : seq, cigar, n_cigar, md);
+      if (al->md_len <= FEMGPU_MD_MAX) { /* the MD text came along as well: no reference access on the host */
+        memcpy(md, al->md, al->md_len);
+        md[al->md_len] = 0;
+      } else {
+        if (m->direction && !have_rc) { make_rc(seq, l, rc); have_rc = 1; }
+        md_text(window + start, m->direction ? rc : seq, cigar, n_cigar, md);
+      }
     } else {
+      if (m->direction && !have_rc) { make_rc(seq, l, rc); have_rc = 1; }
       start = femhost_alignment(window, m->direction ? rc : seq, l, e, m->edit_distance, m->end_position_offset, cigar,
                                 &n_cigar, md);
       if (start == FEMHOST_ALIGN_ERROR) return -2;

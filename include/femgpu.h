@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define FEMGPU_ABI_VERSION 3
+#define FEMGPU_ABI_VERSION 4
 
 typedef enum {
   FEMGPU_OK = 0,
@@ -52,17 +52,19 @@ typedef struct {
   uint8_t reserved[2];
 } femgpu_mapping;
 
-/* Start and CIGAR of one mapping as generate_alignment (src/align.c:279-499) produces them,
- * computed on the device.  40 bytes.  cigar[i] = (length << 2) | op with op 0 M, 1 I, 2 D, in
+/* Start, CIGAR and MD text of one mapping as generate_alignment and generate_MD_tag
+ * (src/align.c:279-544) produce them, computed on the device.  88 bytes.  cigar[i] = (length << 2) | op with op 0 M, 1 I, 2 D, in
  * SAM order.  n_cigar == FEMGPU_ALN_HOST: not computed (a character outside "ACGTN" in the read
  * or the reference -- the reference compares raw characters there); the host's
  * femhost_alignment handles those. */
 #define FEMGPU_ALN_HOST 0xFF
+#define FEMGPU_MD_MAX 47
 typedef struct {
   int16_t start;      /* 0-based, relative to candidate_position (src/align.c:78)           */
   uint8_t n_cigar;
-  uint8_t reserved;
+  uint8_t md_len;     /* characters of md; FEMGPU_ALN_HOST: not computed (longer than FEMGPU_MD_MAX) */
   uint16_t cigar[18];
+  char md[48];        /* the MD text of generate_MD_tag (src/align.c:501-544), not NUL terminated   */
 } femgpu_alignment;
 
 /* One batch of reads: what a SequenceBatch (src/sequence_batch.h:15-24) holds, flattened.

@@ -183,27 +183,32 @@ def test_mappings_match_oracle(setup):
 
 
 def test_device_traceback_matches_oracle(setup):
-    """k_trace: start and CIGAR of every mapping (src/align.c:279-499) against the oracle."""
+    """k_trace: start, CIGAR and MD text of every mapping (src/align.c:279-544) against the oracle."""
     from fem_b200.api import ALN_HOST
     seqs = [r[1] for r in setup.reads[:400]]
     first, maps, _ = setup.mapper.map_batch(seqs, setup.e, setup.a)
     alns = setup.mapper.last_alignments
     assert alns is not None and len(alns) == len(maps)
-    n_dev = 0
+    n_dev = n_md = 0
     for i, seq in enumerate(seqs):
         canonical = set(seq) <= set(b"ACGTN")
         for j in range(int(first[i]), int(first[i + 1])):
             m, al = maps[j], alns[j]
             text = ol.revcomp(seq) if m["direction"] else seq
-            start, cigar, _ = setup.oracle.alignment(int(m["candidate_position"]), text, int(m["edit_distance"]),
-                                                     int(m["end_position_offset"]))
+            start, cigar, md = setup.oracle.alignment(int(m["candidate_position"]), text, int(m["edit_distance"]),
+                                                      int(m["end_position_offset"]))
             if al["n_cigar"] == ALN_HOST:
                 assert not canonical or setup.tag == "withN", "read %d left to the host without need" % i
                 continue
             n_dev += 1
             got = [((int(c) >> 2) << 4) | (int(c) & 3) for c in al["cigar"][:al["n_cigar"]]]
             assert (int(al["start"]), got) == (start, cigar), "read %d mapping %d" % (i, j)
-    assert n_dev > 0
+            if al["md_len"] != ALN_HOST:  # the MD text of src/align.c:501-544 as well
+                n_md += 1
+                assert al["md"][:al["md_len"]].decode() == md and len(md) == al["md_len"], "read %d mapping %d" % (i, j)
+            else:
+                assert len(md) > 47
+    assert n_dev > 0 and n_md > 0
     setup.mapper.set_option("device_traceback", 0)
     try:
         setup.mapper.map_batch(seqs[:50], setup.e, setup.a)
