@@ -61,12 +61,14 @@ template <bool HAS_N>
 __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t *text, const uint16_t *cig, int nc, uint32_t *dst) {
   char md[48];
   int o = 0, tp = 0;
-  uint32_t run = 0;
+  uint32_t run = 0, w2 = 0, wn = 0; // the reference is walked forward: 16 bases per loaded word
+  bool fresh = true;
   for (int ci = 0; ci < nc; ++ci) {
     const uint32_t op = cig[ci] & 3u, len = cig[ci] >> 2;
     if (op == 0) {
       for (uint32_t j = 0; j < len; ++j, ++gref, ++tp) {
-        const uint32_t c = ref_code_fetch<HAS_N>(R, gref);
+        const uint32_t c = ref_code_at<HAS_N>(R, gref, w2, wn, fresh);
+        fresh = false;
         if (c == text[tp]) { ++run; continue; }
         if (run) { o = md_put_uint(md, o, run); run = 0; }
         if (o < 48) md[o] = "ACGTN"[c];
@@ -79,7 +81,9 @@ __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t
       if (o < 48) md[o] = '^';
       ++o;
       for (uint32_t j = 0; j < len; ++j, ++gref) {
-        if (o < 48) md[o] = "ACGTN"[ref_code_fetch<HAS_N>(R, gref)];
+        const uint32_t c = ref_code_at<HAS_N>(R, gref, w2, wn, fresh);
+        fresh = false;
+        if (o < 48) md[o] = "ACGTN"[c];
         ++o;
       }
     }
