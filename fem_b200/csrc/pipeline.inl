@@ -8,7 +8,8 @@ struct Plan { // derived from params + the batch
   uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
   size_t hash_smem;
   uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
-  size_t pair_smem;
+  size_t pair_smem, pair32_smem;
+  bool pair32;
   int first_path; // 0 sort, 1 hash, 2 pair, 3 small
   size_t small_smem;
 };
@@ -63,6 +64,9 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     pl->pair_shift = 32;
     for (uint32_t t = M; t > 1; t >>= 1) --pl->pair_shift;
     pl->pair_smem = 4 * cand_pair_smem_bytes_per_warp(M, VC);
+    pl->pair32_smem = 4 * cand_pair32_smem_bytes_per_warp(M, VC + 64);
+    if (c->pair_layout == 32 && !c->occ32_tried) TRY(derive_occ32_now(c));
+    pl->pair32 = c->occ32_ok && c->pair_layout == 32;
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
   pl->small_smem = 4 * ((cand_small_smem_bytes_per_warp() + 15) & ~(size_t)15);
@@ -176,6 +180,10 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.rs_status = sa.rs_status;
   ca.read_off = sa.read_off;
   ca.rec_len = c->rec_len.as<uint32_t>();
+  ca.occ32 = c->occ32_ok ? c->occ32.as<uint32_t>() : nullptr;
+  ca.gbase = c->gbase.as<uint32_t>();
+  ca.padflag = c->padflag.as<uint32_t>();
+  ca.n_rec = c->n_rec;
   ca.n_rs = (uint32_t)n_rs;
   ca.step = pl.step; ca.e = pl.e; ca.a = pl.a; ca.Q = pl.Q;
   ca.cand_count = &dc->cand_count;
@@ -188,6 +196,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
   if (pl.small_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.small_smem));
+  if (pl.pair32_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair32_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
 
   Counters hc;
@@ -199,6 +208,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.rs_list = nullptr;
     ca.n_list = 0;
     if (pl.first_path == 3) k_cand_small<<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca);
+    else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
     else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
     else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);

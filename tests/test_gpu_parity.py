@@ -23,6 +23,10 @@ CASES = [
     ("e0", [200_000, 100_000], 0.2, 0.0, 600, 100, 0, 1, 12, 3, 0.0),
     ("e1_k10", [100_000, 50_000], 0.1, 0.0, 600, 80, 1, 1, 10, 4, 0.0),
     ("withN", [200_000, 100_000], 0.1, 0.002, 800, 100, 4, 1, 12, 3, 0.004),
+    # many short records: reads at record starts and ends (entries dropped for position < seed offset,
+    # the 32-bit coordinate's pads, the range filter) on nearly every read
+    ("edges_e3_s3", [1500] * 70 + [400, 130, 99, 40], 0.1, 0.0, 900, 100, 3, 1, 12, 3, 0.0),
+    ("edges_e5_s2", [2200] * 50, 0.3, 0.0, 600, 120, 5, 1, 11, 2, 0.0),
 ]
 
 
@@ -111,17 +115,20 @@ def test_candidates_hash_path_table_sizes(setup, slots):
         setup.mapper.set_option("cand_mode", 0)
 
 
+@pytest.mark.parametrize("layout", [32, 64])
 @pytest.mark.parametrize("bits,values", [(1024, 32), (1024, 2048), (4096, 128), (32768, 512), (0, 0)])
-def test_candidates_pair_path_sizes(setup, bits, values):
+def test_candidates_pair_path_sizes(setup, bits, values, layout):
     """k_cand_pair from a crowded bitmap (nearly every entry falsely flagged, most read-strands handed
     on to the sort path) and a tiny value buffer to generous ones; (0, 0) is the automatic plan."""
     seqs = [r[1] for r in setup.reads]
     setup.mapper.set_option("pair_bits", bits)
     setup.mapper.set_option("pair_values", values)
+    setup.mapper.set_option("pair_layout", layout)  # 32: the 32-bit copy of the occurrence table, 64: the table itself
     setup.mapper.set_option("cand_mode", 3)
     try:
         check_candidates(setup, seqs)
     finally:
+        setup.mapper.set_option("pair_layout", 0)
         setup.mapper.set_option("pair_bits", 0)
         setup.mapper.set_option("pair_values", 0)
         setup.mapper.set_option("cand_mode", 0)
