@@ -57,7 +57,12 @@ ALN_HOST = 0xFF
 
 class Result(C.Structure):
     _fields_ = [("first", C.POINTER(C.c_uint64)), ("maps", C.POINTER(MappingRec)), ("stats", Stats),
-                ("alns", C.POINTER(AlignmentRec))]
+                ("alns", C.POINTER(AlignmentRec)),
+                ("sam_text", C.c_void_p), ("sam_off", C.POINTER(C.c_uint64)), ("sam_host", C.POINTER(C.c_uint8))]
+
+
+class SamInputs(C.Structure):
+    _fields_ = [("names", C.c_void_p), ("name_off", C.c_void_p), ("quals", C.c_void_p), ("has_qual", C.c_void_p)]
 
 
 class Candidates(C.Structure):
@@ -84,6 +89,8 @@ EXPORTS = {
     "femgpu_map_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Result)]),
     "femgpu_submit_batch": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Params), C.POINTER(Batch)]),
     "femgpu_wait_batch": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Result)]),
+    "femgpu_set_reference_names": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_char_p)]),
+    "femgpu_set_sam_inputs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(SamInputs)]),
     "femgpu_candidates_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Candidates)]),
     "femgpu_sort_mappings": (None, [C.c_void_p, C.c_size_t]),
     "femgpu_sort_mappings_aln": (None, [C.c_void_p, C.c_void_p, C.c_size_t]),
@@ -214,6 +221,8 @@ class Mapper:
         lens = (C.c_uint32 * n)(*[len(r[1]) for r in records])
         self._keep = (seqs, lens)
         _check(self.lib.femgpu_upload_reference(self.h, n, seqs, lens))
+        names = (C.c_char_p * n)(*[r[0] if isinstance(r[0], bytes) else str(r[0]).encode() for r in records])
+        _check(self.lib.femgpu_set_reference_names(self.h, n, names))
 
     # -- hot path -----------------------------------------------------------------------------
     @staticmethod
@@ -230,7 +239,32 @@ class Mapper:
         # device start/CIGAR per mapping (k_trace), parallel to maps; None when switched off
         self.last_alignments = (np.frombuffer(C.string_at(res.alns, n * 88), dtype=ALIGNMENT_DTYPE).copy()
                                 if n and res.alns else None)
+        # device SAM text (k_sam): per-read byte offsets, host flags, text; None without set_sam_inputs
+        self.last_sam = None
+        if res.sam_off:
+            off = np.ctypeslib.as_array(res.sam_off, shape=(n_reads + 1,)).copy()
+            host = np.ctypeslib.as_array(res.sam_host, shape=(max(n_reads, 1),))[:n_reads].copy()
+            self.last_sam = (off, host, C.string_at(res.sam_text, int(off[-1])) if int(off[-1]) else b"")
         return first, maps, res.stats.as_tuple()
+
+    def set_sam_inputs(self, slot, names, quals):
+        """names: list of bytes; quals: list of bytes (same lengths as the reads) or None per read.
+        Applies to the next submit/map_batch on the slot (map_batch uses slot 0)."""
+        n = len(names)
+        name_off = np.zeros(n + 1, dtype=np.uint64)
+        np.cumsum(np.fromiter((len(x) + 1 for x in names), dtype=np.uint64, count=n), out=name_off[1:])
+        nm = np.frombuffer(b"".join(x + b"\0" for x in names) or b"\0", dtype=np.uint8)
+        has = np.fromiter((q is not None for q in quals), dtype=np.uint8, count=n)
+        return nm, name_off, has
+
+    def map_batch_sam(self, reads, names, quals, e, a=1, k=0, step=0):
+        """map_batch with the SAM text formatted on the device: -> (first, maps, stats); text in last_sam."""
+        b = ReadBatch(reads)
+        nm, name_off, has = self.set_sam_inputs(0, names, quals)
+        q = np.frombuffer(b"".join(qq if qq is not None else b" " * len(r) for qq, r in zip(quals, reads)) or b" ", dtype=np.uint8)
+        si = SamInputs(nm.ctypes.data, name_off.ctypes.data, q.ctypes.data, has.ctypes.data)
+        _check(self.lib.femgpu_set_sam_inputs(self.h, 0, C.byref(si)))
+        return self.map_batch(b, e, a, k, step)
 
     def map_batch(self, reads, e, a=1, k=0, step=0):
         """-> (first[n+1], maps (structured array, emission order), stats tuple)"""

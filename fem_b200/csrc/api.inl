@@ -36,6 +36,73 @@ static int stage_batch(femgpu_ctx *c, Slot &s, const femgpu_params *p, const fem
     CU(cudaMemcpyAsync(s.bases.p, b->bases, n_bases, cudaMemcpyHostToDevice, s.stream));
     CU(cudaMemcpyAsync(s.read_off.p, b->offsets, (b->n_reads + 1ull) * 8, cudaMemcpyHostToDevice, s.stream));
   }
+  // SAM text inputs apply to this submit only
+  s.sam_on = s.sam_pending && c->device_traceback && c->have_rnames && b->n_reads > 0;
+  s.sam_pending = false;
+  if (s.sam_on) {
+    const femgpu_sam_inputs &in = s.sam_in;
+    const uint64_t name_bytes = in.name_off[b->n_reads];
+    TRY(s.names.reserve(name_bytes + 16));
+    TRY(s.name_off.reserve((b->n_reads + 1ull) * 8));
+    TRY(s.quals.reserve(n_bases + 16));
+    TRY(s.has_qual.reserve(b->n_reads + 16ull));
+    CU(cudaMemcpyAsync(s.names.p, in.names, name_bytes, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.name_off.p, in.name_off, (b->n_reads + 1ull) * 8, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.quals.p, in.quals, n_bases, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.has_qual.p, in.has_qual, b->n_reads, cudaMemcpyHostToDevice, s.stream));
+  }
+  return 0;
+}
+
+// k_sam: lengths -> exclusive scan over reads -> text.  After run_verify_and_compact (needs k_trace).
+static int run_sam(femgpu_ctx *c, Slot &s) {
+  s.sam_total = 0;
+  s.sam_flagged = 0;
+  if (!s.sam_on) return 0;
+  const uint32_t n = s.n_reads;
+  Counters *dc = s.counters.as<Counters>();
+  TRY(s.sam_bytes.reserve(n * 4ull + 16));
+  TRY(s.sam_host.reserve(n + 16ull));
+  TRY(s.sam_off.reserve((n + 1ull) * 8));
+  const unsigned n_blocks = (unsigned)((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
+  TRY(s.sam_blocks.reserve((n_blocks + 2ull) * 8));
+  SamArgs a;
+  a.bases = s.bases.as<char>();
+  a.read_off = s.read_off.as<uint64_t>();
+  a.n_reads = n;
+  a.quals = s.quals.as<char>();
+  a.has_qual = s.has_qual.as<uint8_t>();
+  a.names = s.names.as<char>();
+  a.name_off = s.name_off.as<uint64_t>();
+  a.rnames = c->rnames.as<char>();
+  a.rname_off = c->rname_off.as<uint32_t>();
+  a.maps = s.maps.as<ulonglong2>();
+  a.aln = s.aln.as<uint32_t>();
+  a.rs_map_first = s.rs_map_first.as<uint64_t>();
+  a.read_bytes = s.sam_bytes.as<uint32_t>();
+  a.host_flag = s.sam_host.as<uint8_t>();
+  a.text_off = s.sam_off.as<uint64_t>();
+  a.n_flagged = &dc->sam_flagged;
+  a.text = nullptr;
+  const unsigned grid = (n + 127) / 128;
+  k_sam<false><<<grid, 128, 0, s.stream>>>(a);
+  k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>());
+  k_scan_blocks<<<1, 32, 0, s.stream>>>(s.sam_blocks.as<uint64_t>(), n_blocks, (uint64_t *)&dc->sam_total);
+  k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>(),
+                                                     s.sam_off.as<uint64_t>(), (uint64_t *)&dc->sam_total);
+  s.n_launches += 4;
+  CU(cudaGetLastError());
+  Counters hc;
+  TRY(read_counters(s, &hc));
+  s.sam_total = hc.sam_total;
+  s.sam_flagged = hc.sam_flagged;
+  if (s.sam_total) {
+    TRY(s.sam_text.reserve(s.sam_total + 16));
+    a.text = s.sam_text.as<char>();
+    k_sam<true><<<grid, 128, 0, s.stream>>>(a);
+    ++s.n_launches;
+    CU(cudaGetLastError());
+  }
   return 0;
 }
 
@@ -50,10 +117,19 @@ static int fetch_result(Slot &s, femgpu_result *r) {
     if (s.n_maps) {
       TRY(s.h_maps.reserve(s.n_maps * 16));
       CU(cudaMemcpyAsync(s.h_maps.p, s.maps.p, s.n_maps * 16, cudaMemcpyDeviceToHost, s.stream));
+      if (s.has_aln && s.sam_on && s.sam_flagged == 0) s.has_aln = false; // every record is already text
       if (s.has_aln) {
         TRY(s.h_aln.reserve(s.n_maps * sizeof(femgpu_alignment)));
         CU(cudaMemcpyAsync(s.h_aln.p, s.aln.p, s.n_maps * sizeof(femgpu_alignment), cudaMemcpyDeviceToHost, s.stream));
       }
+    }
+    if (s.sam_on) {
+      TRY(s.h_sam_off.reserve((n + 1ull) * 8));
+      TRY(s.h_sam_host.reserve(n + 16ull));
+      TRY(s.h_sam_text.reserve(s.sam_total + 16));
+      CU(cudaMemcpyAsync(s.h_sam_off.p, s.sam_off.p, (n + 1ull) * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaMemcpyAsync(s.h_sam_host.p, s.sam_host.p, n, cudaMemcpyDeviceToHost, s.stream));
+      if (s.sam_total) CU(cudaMemcpyAsync(s.h_sam_text.p, s.sam_text.p, s.sam_total, cudaMemcpyDeviceToHost, s.stream));
     }
     // infeasible read-strands are rare; count them from the status bytes
     TRY(s.h_status.reserve(2ull * n));
@@ -81,6 +157,10 @@ static int fetch_result(Slot &s, femgpu_result *r) {
     r->maps = s.h_maps.as<femgpu_mapping>();
     r->alns = s.has_aln && s.n_maps ? s.h_aln.as<femgpu_alignment>() : nullptr;
     r->stats = s.stats;
+    const bool sam = s.sam_on && n > 0;
+    r->sam_text = sam ? s.h_sam_text.as<char>() : nullptr;
+    r->sam_off = sam ? s.h_sam_off.as<uint64_t>() : nullptr;
+    r->sam_host = sam ? s.h_sam_host.as<uint8_t>() : nullptr;
   }
   return 0;
 }
@@ -97,8 +177,38 @@ extern "C" int femgpu_submit_batch(femgpu_ctx *c, int slot, const femgpu_params 
   TRY(run_seed_and_candidates(c, s, pl));
   TRY(run_verify_and_compact(c, s, pl));
   s.has_aln = c->device_traceback != 0;
+  TRY(run_sam(c, s));
   s.busy = true;
   c->last_slot = slot;
+  return 0;
+}
+
+extern "C" int femgpu_set_sam_inputs(femgpu_ctx *c, int slot, const femgpu_sam_inputs *in) {
+  if (!c || slot < 0 || slot > 1) return set_error(FEMGPU_EINVAL, "bad context or slot");
+  Slot &s = c->slot[slot];
+  if (!in) { s.sam_pending = false; return 0; }
+  if (!in->names || !in->name_off || !in->quals || !in->has_qual) return set_error(FEMGPU_EINVAL, "null SAM input");
+  s.sam_in = *in;
+  s.sam_pending = true;
+  return 0;
+}
+
+extern "C" int femgpu_set_reference_names(femgpu_ctx *c, uint32_t n_records, const char *const *names) {
+  if (!c || !names) return set_error(FEMGPU_EINVAL, "null argument");
+  if (!c->n_rec || n_records != c->n_rec) return set_error(FEMGPU_ESTATE, "reference names must follow femgpu_upload_reference (%u records resident)", c->n_rec);
+  CU(cudaSetDevice(c->device));
+  std::vector<uint32_t> off(n_records + 1, 0);
+  std::string all;
+  for (uint32_t i = 0; i < n_records; ++i) {
+    if (!names[i]) return set_error(FEMGPU_EINVAL, "null record name");
+    all += names[i];
+    off[i + 1] = (uint32_t)all.size();
+  }
+  TRY(c->rnames.reserve(all.size() + 16));
+  TRY(c->rname_off.reserve((n_records + 1ull) * 4));
+  CU(cudaMemcpy(c->rnames.p, all.data(), all.size(), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(c->rname_off.p, off.data(), (n_records + 1ull) * 4, cudaMemcpyHostToDevice));
+  c->have_rnames = true;
   return 0;
 }
 

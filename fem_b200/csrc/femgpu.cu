@@ -24,6 +24,7 @@
 #include "k_peak.cuh"
 #include "k_seed.cuh"
 #include "k_trace.cuh"
+#include "k_sam.cuh"
 #include "k_verify.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -102,6 +103,8 @@ struct Counters {
   unsigned long long total_before;
   unsigned long long total_maps;
   unsigned long long cols_executed;
+  unsigned long long sam_total;
+  unsigned long long sam_flagged; // reads k_sam left to the host
   uint32_t overflow_count;
   int error_flag;
 };
@@ -117,12 +120,19 @@ struct Slot {
   DBuf read_flags, map_rs, aln;
   DBuf big_list, big_off, big_S, big_A, scratch, hash_list;
   DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
+  // SAM text on the device (k_sam): inputs of the batch, per-read sizes / offsets / flags, the text
+  DBuf names, name_off, quals, has_qual, sam_bytes, sam_host, sam_off, sam_blocks, sam_text;
+  HBuf h_sam_text, h_sam_off, h_sam_host;
+  femgpu_sam_inputs sam_in{};
+  bool sam_pending = false, sam_on = false;
+  uint64_t sam_total = 0;
   HBuf h_aln;
   HBuf h_counters, h_first, h_maps, h_overflow, h_plan, h_cands, h_before, h_status;
   uint64_t cand_cap = 0;
   // state of the batch in flight
   bool busy = false;
   bool has_aln = false;
+  uint64_t sam_flagged = 0;
   femgpu_params params{};
   uint32_t n_reads = 0;
   uint64_t n_bases = 0;
@@ -149,6 +159,8 @@ struct femgpu_ctx {
   int idx_k = 0, idx_step = 0;
   // reference
   DBuf ref2, refn, rec_base, rec_len;
+  DBuf rnames, rname_off;     // record names for k_sam (femgpu_set_reference_names)
+  bool have_rnames = false;
   uint32_t n_rec = 0;
   uint64_t ref_total = 0;
   bool ref_has_n = false;
@@ -207,9 +219,10 @@ static void slot_release(Slot &s) {
   DBuf *d[] = {&s.bases, &s.read_off, &s.codes, &s.rs_status, &s.rs_before, &s.rs_max_f, &s.rs_sum_f, &s.seed_begin,
                &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
                &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
-               &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first};
+               &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first,
+               &s.names, &s.name_off, &s.quals, &s.has_qual, &s.sam_bytes, &s.sam_host, &s.sam_off, &s.sam_blocks, &s.sam_text};
   for (auto *b : d) b->release();
-  HBuf *h[] = {&s.h_aln, &s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
+  HBuf *h[] = {&s.h_sam_text, &s.h_sam_off, &s.h_sam_host, &s.h_aln, &s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
   for (auto *b : h) b->release();
   for (auto &e : s.ev) if (e) cudaEventDestroy(e);
   if (s.stream) cudaStreamDestroy(s.stream);
@@ -220,7 +233,7 @@ extern "C" void femgpu_destroy(femgpu_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto &s : c->slot) slot_release(s);
-  c->lut.release(); c->occ.release(); c->occ32.release(); c->gbase.release(); c->padflag.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release();
+  c->lut.release(); c->occ.release(); c->occ32.release(); c->gbase.release(); c->padflag.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
   delete c;
 }
 

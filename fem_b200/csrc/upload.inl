@@ -152,6 +152,7 @@ extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char
   cleanup(0);
   if (err != cudaSuccess) return set_error(FEMGPU_ECUDA, "reference upload failed: %s", cudaGetErrorString(err));
   c->n_rec = n_rec;
+  c->have_rnames = false; // names belong to the previous reference
   c->ref_total = total;
   c->ref_has_n = (any_n & 1) != 0;
   c->ref_canonical = (any_n & 2) == 0;

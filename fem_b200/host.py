@@ -43,7 +43,7 @@ class MapOptions(C.Structure):
 class MapTiming(C.Structure):
     _fields_ = [("wall", C.c_double), ("parse", C.c_double), ("gpu_wait", C.c_double), ("format", C.c_double),
                 ("write", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("sam_bytes", C.c_uint64),
-                ("n_batches", C.c_uint32), ("n_launches", C.c_uint32)]
+                ("n_batches", C.c_uint32), ("n_launches", C.c_uint32), ("device_sam_reads", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

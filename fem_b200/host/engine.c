@@ -112,6 +112,12 @@ femhost_mapper *femhost_mapper_create(const char *ref_path, const char *index_pa
     rc = n_gpus > 1 ? femgpu_upload_index(m->ctx[g], idx.k, idx.step, idx.lut, idx.lut_n, idx.occ, idx.n_occ)
                     : femgpu_upload_index_file(m->ctx[g], index_path);
     if (!rc) rc = femgpu_upload_reference(m->ctx[g], m->ref.n_records, seqs, lens);
+    if (!rc) { /* record names for the device's SAM text (k_sam) */
+      const char **rn = (const char **)malloc(m->ref.n_records * sizeof(char *));
+      for (uint32_t i = 0; i < m->ref.n_records; ++i) rn[i] = femhost_record_name(&m->ref, i);
+      rc = femgpu_set_reference_names(m->ctx[g], m->ref.n_records, rn);
+      free(rn);
+    }
     const char *tb = getenv("FEM_DEVICE_TRACEBACK"); /* "0": start/CIGAR of every mapping on the host */
     if (!rc && tb) rc = femgpu_set_option(m->ctx[g], "device_traceback", atoi(tb));
     if (rc) femhost_set_error(rc, "%s", femgpu_last_error());
@@ -173,6 +179,8 @@ typedef struct {
   uint32_t chunk;
   int write;                /* 0: build the chunk's SAM text; 1: pwrite it at file_off */
   uint64_t file_off;
+  const char *ext;          /* the chunk's text as the device formatted it (NULL: b->text[chunk]) */
+  size_t ext_len;
 } work_item;
 struct batch {
   uint64_t seq;             /* position in file order */
@@ -181,6 +189,12 @@ struct batch {
   femgpu_mapping *maps;
   femgpu_alignment *alns;   /* NULL-able: device start/CIGAR per mapping */
   int has_alns;
+  char *sam_text;           /* copy of the device's SAM text (k_sam), NULL-able */
+  uint64_t *sam_off;        /* n_reads + 1 */
+  uint8_t *sam_host;        /* n_reads: 1 = this read is formatted here */
+  int has_sam;
+  uint64_t sam_dev_reads;   /* mapped reads of the batch the device formatted */
+  size_t cap_sam_text, cap_sam_reads;
   size_t cap_first, cap_maps, cap_alns;
   femgpu_stats stats;
   uint32_t n_launches;
@@ -202,6 +216,7 @@ static void pool_free(femhost_mapper *m) {
     free(b->first);
     free(b->maps);
     free(b->alns);
+    free(b->sam_text); free(b->sam_off); free(b->sam_host);
     for (size_t c = 0; c < b->cap_chunks; ++c) femhost_str_free(&b->text[c]);
     free(b->text);
     free(b->items);
@@ -218,6 +233,7 @@ typedef struct {
   int out_fd;               /* -1: build the text, write nothing */
   int out_seekable;         /* regular file: chunks are written in parallel with pwrite */
   uint64_t out_off;         /* next file offset (writer thread only) */
+  int device_sam;           /* SAM text formatted by k_sam (FEM_DEVICE_SAM=0: on the host) */
   int out_populate;         /* madvise(MADV_POPULATE_WRITE) before the copy (FEM_SAM_POPULATE=0 turns it off) */
   int out_mmap;             /* tmpfs: chunks are copied into a shared mapping (pwrite holds the inode lock) */
   uint64_t out_alloc;       /* size the file has been extended to (writer thread only) */
@@ -382,7 +398,12 @@ static void *gpu_main(void *arg) {
       const double t0 = femhost_now();
       femgpu_batch gb = {b->reads.bases, b->reads.base_off, n};
       femgpu_result res;
-      int rc = femgpu_submit_batch(ctx, ga->slot, &r->opt->params, &gb);
+      int rc = 0;
+      if (r->device_sam && n && b->reads.quals && b->reads.has_qual) {
+        femgpu_sam_inputs si = {b->reads.names, b->reads.name_off, b->reads.quals, b->reads.has_qual};
+        rc = femgpu_set_sam_inputs(ctx, ga->slot, &si);
+      }
+      if (!rc) rc = femgpu_submit_batch(ctx, ga->slot, &r->opt->params, &gb);
       if (!rc) rc = femgpu_wait_batch(ctx, ga->slot, &res);
       if (rc) { run_fail(r, femgpu_last_error()); ok = 0; }
       else {
@@ -395,6 +416,21 @@ static void *gpu_main(void *arg) {
         if (res.alns) {
           if (n_maps > b->cap_alns) { b->cap_alns = n_maps + n_maps / 4 + 1024; b->alns = (femgpu_alignment *)realloc(b->alns, b->cap_alns * sizeof(femgpu_alignment)); }
           memcpy(b->alns, res.alns, n_maps * sizeof(femgpu_alignment));
+        }
+        b->has_sam = res.sam_off != NULL;
+        if (b->has_sam) {
+          const uint64_t nb = res.sam_off[n];
+          if ((size_t)n + 1 > b->cap_sam_reads) {
+            b->cap_sam_reads = (size_t)n + 1;
+            b->sam_off = (uint64_t *)realloc(b->sam_off, b->cap_sam_reads * 8);
+            b->sam_host = (uint8_t *)realloc(b->sam_host, b->cap_sam_reads);
+          }
+          if (nb > b->cap_sam_text) { b->cap_sam_text = nb + nb / 8 + 4096; b->sam_text = (char *)realloc(b->sam_text, b->cap_sam_text); }
+          memcpy(b->sam_off, res.sam_off, ((size_t)n + 1) * 8);
+          memcpy(b->sam_host, res.sam_host, n);
+          memcpy(b->sam_text, res.sam_text, nb);
+          b->sam_dev_reads = 0;
+          for (uint32_t i = 0; i < n; ++i) b->sam_dev_reads += b->sam_off[i + 1] > b->sam_off[i];
         }
         b->stats = res.stats;
         float ms[6];
@@ -418,6 +454,8 @@ static void *gpu_main(void *arg) {
       b->items[c].b = b;
       b->items[c].chunk = c;
       b->items[c].write = 0;
+      b->items[c].ext = NULL;
+      b->items[c].ext_len = 0;
       fifo_push(&r->q_work, &b->items[c]);
     }
   }
@@ -455,13 +493,14 @@ static void *worker_main(void *arg) {
 #ifndef MADV_POPULATE_WRITE
 #define MADV_POPULATE_WRITE 23
 #endif
-        if (r->out_populate && out->l) { /* all pages of the chunk in one call instead of one fault each */
+        const size_t wl = it->ext ? it->ext_len : out->l;
+        if (r->out_populate && wl) { /* all pages of the chunk in one call instead of one fault each */
           const uintptr_t pg = (uintptr_t)sysconf(_SC_PAGESIZE), p0 = (uintptr_t)dst & ~(pg - 1);
-          madvise((void *)p0, (size_t)((uintptr_t)dst + out->l - p0), MADV_POPULATE_WRITE);
+          madvise((void *)p0, (size_t)((uintptr_t)dst + wl - p0), MADV_POPULATE_WRITE);
         }
-        memcpy(dst, out->s, out->l);
+        memcpy(dst, it->ext ? it->ext : out->s, it->ext ? it->ext_len : out->l);
       }
-      else if (write_all(r->out_fd, out->s, out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
+      else if (write_all(r->out_fd, it->ext ? it->ext : out->s, it->ext ? it->ext_len : out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
       pthread_mutex_lock(&r->mu);
       const int left = --b->writes_left;
       pthread_mutex_unlock(&r->mu);
@@ -476,15 +515,28 @@ static void *worker_main(void *arg) {
     out->l = 0;
     const uint32_t lo = it->chunk * CHUNK_READS;
     const uint32_t hi = lo + CHUNK_READS < b->reads.n_records ? lo + CHUNK_READS : b->reads.n_records;
+    if (b->has_sam && !memchr(b->sam_host + lo, 1, hi - lo)) { /* the device formatted every read of the chunk */
+      it->ext = b->sam_text + b->sam_off[lo];
+      it->ext_len = (size_t)(b->sam_off[hi] - b->sam_off[lo]);
+      goto chunk_done;
+    }
     for (uint32_t i = lo; i < hi && !r->failed; ++i) {
       const size_t n = (size_t)(b->first[i + 1] - b->first[i]);
       if (!n) continue;
+      if (b->has_sam && !b->sam_host[i]) { /* this read's records as the device wrote them */
+        const size_t tl = (size_t)(b->sam_off[i + 1] - b->sam_off[i]);
+        if (femhost_str_reserve(out, tl)) { run_fail(r, femhost_last_error()); break; }
+        memcpy(out->s + out->l, b->sam_text + b->sam_off[i], tl);
+        out->l += tl;
+        continue;
+      }
       const uint64_t off = b->reads.base_off[i];
       if (femhost_sam_read(ref, femhost_record_name(&b->reads, i), b->reads.bases + off,
                            b->reads.has_qual[i] ? b->reads.quals + off : no_qual, (int)femhost_record_length(&b->reads, i), e,
                            b->maps + b->first[i], b->has_alns ? b->alns + b->first[i] : NULL, n, out))
         run_fail(r, femhost_last_error());
     }
+  chunk_done:
     wa->busy += femhost_now() - t0;
     pthread_mutex_lock(&r->mu);
     const int left = --b->chunks_left;
@@ -511,11 +563,11 @@ static void *writer_main(void *arg) {
     const double t0 = femhost_now();
     int n_writes = 0;
     for (uint32_t c = 0; c < b->n_chunks; ++c) {
-      const size_t len = b->text[c].l;
+      const size_t len = b->items[c].ext ? b->items[c].ext_len : b->text[c].l;
       r->tm.sam_bytes += len;
       if (r->out_fd < 0 || !len) continue;
       if (!r->out_seekable) { /* pipe: in order, from this thread */
-        if (write_all(r->out_fd, b->text[c].s, len, 0, 0)) run_fail(r, "short write to the SAM file");
+        if (write_all(r->out_fd, b->items[c].ext ? b->items[c].ext : b->text[c].s, len, 0, 0)) run_fail(r, "short write to the SAM file");
         continue;
       }
       b->items[c].write = 1;
@@ -555,9 +607,12 @@ static void *writer_main(void *arg) {
     r->stats.num_candidates += b->stats.num_candidates;
     r->stats.num_mappings += b->stats.num_mappings;
     r->stats.num_infeasible_reads += b->stats.num_infeasible_reads;
-    r->tm.h2d_bytes += b->reads.n_bases + ((uint64_t)b->reads.n_records + 1) * 8;
-    r->tm.d2h_bytes += ((uint64_t)b->reads.n_records + 1) * 8 + b->stats.num_mappings * (sizeof(femgpu_mapping) + (b->has_alns ? sizeof(femgpu_alignment) : 0)) + 2ull * b->reads.n_records;
+    r->tm.h2d_bytes += b->reads.n_bases + ((uint64_t)b->reads.n_records + 1) * 8 +
+                       (b->has_sam ? b->reads.n_bases + b->reads.name_off[b->reads.n_records] + 9ull * b->reads.n_records : 0);
+    r->tm.d2h_bytes += ((uint64_t)b->reads.n_records + 1) * 8 + b->stats.num_mappings * (sizeof(femgpu_mapping) + (b->has_alns ? sizeof(femgpu_alignment) : 0)) + 2ull * b->reads.n_records +
+                       (b->has_sam ? b->sam_off[b->reads.n_records] + 9ull * b->reads.n_records : 0);
     r->tm.n_launches += b->n_launches;
+    if (b->has_sam) r->tm.device_sam_reads += b->sam_dev_reads;
     ++r->tm.n_batches;
     ++next;
     if (!n_writes) fifo_push(&r->q_free, b);
@@ -607,6 +662,7 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     r.rd = femhost_reader_open(reads_path);
     if (!r.rd) return -1;
   }
+  r.device_sam = !(getenv("FEM_DEVICE_SAM") && atoi(getenv("FEM_DEVICE_SAM")) == 0);
   r.out_fd = -1;
   if (sam_path) {
     r.out_fd = open(sam_path, O_RDWR | O_CREAT | O_TRUNC, 0644);

@@ -46,8 +46,8 @@ int femhost_records_reserve(femhost_records *r, size_t n_records, size_t n_bases
     size_t m = r->cap_records ? r->cap_records : 1024;
     while (m < n_records + 1) m *= 2;
     uint64_t *bo = (uint64_t *)grow(r->base_off, r->cap_records * 8, m * 8, r->pinned);
-    uint64_t *no = (uint64_t *)realloc(r->name_off, m * 8);
-    uint8_t *hq = (uint8_t *)realloc(r->has_qual, m);
+    uint64_t *no = (uint64_t *)grow(r->name_off, r->cap_records * 8, m * 8, r->pinned);
+    uint8_t *hq = (uint8_t *)grow(r->has_qual, r->cap_records, m, r->pinned);
     if (bo) r->base_off = bo;
     if (no) r->name_off = no;
     if (hq) r->has_qual = hq;
@@ -59,7 +59,7 @@ int femhost_records_reserve(femhost_records *r, size_t n_records, size_t n_bases
     size_t m = r->cap_bases ? r->cap_bases : (1u << 16);
     while (m < n_bases) m *= 2;
     char *b = (char *)grow(r->bases, r->cap_bases, m, r->pinned);
-    char *q = (char *)realloc(r->quals, m);
+    char *q = (char *)grow(r->quals, r->cap_bases, m, r->pinned);
     if (b) r->bases = b;
     if (q) r->quals = q;
     if (!b || !q) return femhost_set_error(-3, "out of memory (%zu bases)", m);
@@ -68,7 +68,7 @@ int femhost_records_reserve(femhost_records *r, size_t n_records, size_t n_bases
   if (n_names > r->cap_names) {
     size_t m = r->cap_names ? r->cap_names : (1u << 14);
     while (m < n_names) m *= 2;
-    char *nm = (char *)realloc(r->names, m);
+    char *nm = (char *)grow(r->names, r->cap_names, m, r->pinned);
     if (!nm) return femhost_set_error(-3, "out of memory (%zu name bytes)", m);
     r->names = nm;
     r->cap_names = m;
@@ -77,9 +77,13 @@ int femhost_records_reserve(femhost_records *r, size_t n_records, size_t n_bases
 }
 
 void femhost_records_free(femhost_records *r) {
-  if (r->pinned) { femgpu_free_pinned(r->bases); femgpu_free_pinned(r->base_off); }
-  else { free(r->bases); free(r->base_off); }
-  free(r->quals); free(r->has_qual); free(r->names); free(r->name_off);
+  if (r->pinned) { /* names and qualities too: the device's SAM text reads them (femgpu_set_sam_inputs) */
+    femgpu_free_pinned(r->bases); femgpu_free_pinned(r->base_off);
+    femgpu_free_pinned(r->quals); femgpu_free_pinned(r->has_qual); femgpu_free_pinned(r->names); femgpu_free_pinned(r->name_off);
+  } else {
+    free(r->bases); free(r->base_off);
+    free(r->quals); free(r->has_qual); free(r->names); free(r->name_off);
+  }
   int pinned = r->pinned;
   memset(r, 0, sizeof *r);
   r->pinned = pinned;

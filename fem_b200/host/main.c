@@ -164,8 +164,8 @@ static int map_main(int argc, char **argv) {
   fprintf(stderr, "The number of candidate: %" PRIu64 "\n", st.num_candidates);
   fprintf(stderr, "The number of mapping: %" PRIu64 "\n", st.num_mappings);
   fprintf(stderr, "Time: %fs\n", tm.wall);
-  fprintf(stderr, "[phases] parse %.3fs, gpu threads %.3fs, SAM text %.3fs over %d threads, write %.3fs; %u batches, %u kernel launches\n",
-          tm.parse, tm.gpu_wait, tm.format, opt.n_threads, tm.write, tm.n_batches, tm.n_launches);
+  fprintf(stderr, "[phases] parse %.3fs, gpu threads %.3fs, SAM text %.3fs over %d threads, write %.3fs; %u batches, %u kernel launches, %" PRIu64 " reads formatted on the device\n",
+          tm.parse, tm.gpu_wait, tm.format, opt.n_threads, tm.write, tm.n_batches, tm.n_launches, tm.device_sam_reads);
   femhost_mapper_destroy(m);
   return 0;
 }

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define FEMGPU_ABI_VERSION 4
+#define FEMGPU_ABI_VERSION 5
 
 typedef enum {
   FEMGPU_OK = 0,
@@ -97,7 +97,25 @@ typedef struct {
   const femgpu_mapping *maps; /* first[n_reads] records */
   femgpu_stats stats;         /* this batch only */
   const femgpu_alignment *alns; /* parallel to maps; NULL when "device_traceback" is off */
+  /* SAM text formatted on the device (femgpu_set_sam_inputs before the submit): the records of read i,
+   * in the reference's order (src/align.c:56-92), are sam_text[sam_off[i] .. sam_off[i+1]).  Reads with
+   * sam_host[i] != 0 were left to the host (more than 64 mappings: src/ksort.h's unstable radix order;
+   * a character outside "ACGTN"; an MD text longer than FEMGPU_MD_MAX) and own no bytes.  NULL
+   * when no inputs were set. */
+  const char *sam_text;
+  const uint64_t *sam_off;  /* n_reads + 1 */
+  const uint8_t *sam_host;  /* n_reads */
 } femgpu_result;
+
+/* What the SAM records need beyond the bases (src/align.c:546-632 reads them from the kseq record):
+ * names[name_off[i]..] NUL terminated; quals share the batch's offsets, has_qual[i] == 0 prints '*'.
+ * Host memory, valid until the submit returns. */
+typedef struct {
+  const char *names;
+  const uint64_t *name_off; /* n_reads + 1 */
+  const char *quals;
+  const uint8_t *has_qual;  /* n_reads */
+} femgpu_sam_inputs;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */
 int femgpu_abi_version(void);
@@ -162,6 +180,12 @@ int femgpu_map_batch(femgpu_ctx *ctx, const femgpu_params *params, const femgpu_
 int femgpu_submit_batch(femgpu_ctx *ctx, int slot, const femgpu_params *params,
                         const femgpu_batch *batch);
 int femgpu_wait_batch(femgpu_ctx *ctx, int slot, femgpu_result *result);
+/* SAM text on the device (stands in for process_mappings + generate_bam1_t + sam_write1,
+ * src/align.c:56-92,546-632, htslib sam.c:3004-3061).  femgpu_set_reference_names once after
+ * femgpu_upload_reference (names as femhost_sam_header prints them); femgpu_set_sam_inputs applies to
+ * the NEXT submit on that slot only. */
+int femgpu_set_reference_names(femgpu_ctx *ctx, uint32_t n_records, const char *const *names);
+int femgpu_set_sam_inputs(femgpu_ctx *ctx, int slot, const femgpu_sam_inputs *inputs);
 
 /* Stage-level entry points (tests, profiling, and callers that keep their own verification).
  * Candidates: generate_group_seeding_candidates (src/filter.c:146-223) for both strands of every

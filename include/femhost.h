@@ -132,6 +132,7 @@ typedef struct {
   double wall, parse, gpu_wait, format, write;
   uint64_t h2d_bytes, d2h_bytes, sam_bytes;
   uint32_t n_batches, n_launches;
+  uint64_t device_sam_reads; /* mapped reads whose records the device formatted (k_sam) */
 } femhost_map_timing;
 
 /* src/FEM_map.c:172-219, the reference's "Time:" window: read the FASTQ, map, write the SAM file

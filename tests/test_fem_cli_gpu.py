@@ -101,16 +101,18 @@ def test_read_shards_concatenate_to_the_whole(big):
     """One process per GPU: contiguous read shards, outputs concatenated in shard order (8e)."""
     from fem_b200.host import HostMapper
     m = HostMapper(big["fa"], big["idx"], 1)
-    n, parts, total = big["n_reads"], [], [0] * 5
+    n, parts, total, n_dev = big["n_reads"], [], [0] * 5, 0
     cuts = [0, n // 3, n // 3 + 1, n]
     for r in range(3):
         out = str(big["d"] / ("shard%d.sam" % r))
         st, _ = m.map_file(big["fq"], out, big["e"], big["a"], threads=4, batch_reads=997, skip_reads=cuts[r],
                            max_reads=cuts[r + 1] - cuts[r], no_header=r > 0)
         total = [x + y for x, y in zip(total, st[:5])]
+        n_dev += _["device_sam_reads"]
         with open(out, "rb") as f:
             parts.append(f.read())
     m.close()
+    assert n_dev > 0  # k_sam wrote records (the host only formats what it leaves)
     assert b"".join(parts) == big["want"]
     assert tuple(total) == big["counters"]
 
@@ -145,6 +147,7 @@ def test_reader_paths_agree(big):
             if os.path.exists(shm):
                 os.remove(shm)
     assert run(big["fq"], {"FEM_DEVICE_TRACEBACK": "0"}) == big["want"]  # every alignment on the host
+    assert run(big["fq"], {"FEM_DEVICE_SAM": "0"}) == big["want"]  # device alignments, text built on the host
     # sequences wrapped over two lines: not four-line FASTQ -> the run restarts with the kseq reader
     wrapped = str(d / "wrapped.fq")
     with open(big["fq"], "rb") as f, open(wrapped, "wb") as g:

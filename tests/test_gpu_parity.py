@@ -224,6 +224,46 @@ def test_device_traceback_matches_oracle(setup):
         setup.mapper.set_option("device_traceback", 1)
 
 
+def test_device_sam_text_matches_oracle(setup, tmp_path):
+    """k_sam: the records of every read the device formats (order, flags, SEQ/QUAL, NM, MD) are the
+    oracle's SAM lines for that read; reads it leaves to the host own no bytes and are few."""
+    reads = [(n, q, bytes(33 + (i * 7 + j * 3) % 61 for j in range(len(q)))) for i, (n, q, _) in enumerate(setup.reads[:700])]
+    fq, want_sam = str(tmp_path / "r.fq"), str(tmp_path / "want.sam")
+    synth.write_fastq(fq, reads)
+    setup.oracle.map_file(fq, want_sam)
+    want = {}
+    with open(want_sam, "rb") as f:
+        for line in f:
+            if not line.startswith(b"@"):
+                want.setdefault(line.split(b"\t", 1)[0], []).append(line)
+    seqs, names = [r[1] for r in reads], [r[0].encode() for r in reads]
+    quals = [r[2] if i % 7 else None for i, r in enumerate(reads)]  # some FASTA-like reads: QUAL '*'
+    first, maps, _ = setup.mapper.map_batch_sam(seqs, names, quals, setup.e, setup.a)
+    assert setup.mapper.last_sam is not None
+    off, host, text = setup.mapper.last_sam
+    assert len(text) == int(off[-1])
+    n_dev = n_host = 0
+    for i, name in enumerate(names):
+        got = text[int(off[i]):int(off[i + 1])]
+        n = int(first[i + 1] - first[i])
+        if host[i]:
+            assert got == b"" and (n > 64 or not set(seqs[i]) <= set(b"ACGTN") or setup.tag == "withN"), "read %d" % i
+            n_host += 1
+            continue
+        exp = b"".join(want.get(name, []))
+        if quals[i] is None and n:  # the oracle's file carried qualities for every read
+            lines = exp.split(b"\n")
+            f0 = lines[0].split(b"\t")
+            f0[10] = b"*"
+            exp = b"\n".join([b"\t".join(f0)] + lines[1:])
+        assert got == exp, "read %d: %r != %r" % (i, got[:300], exp[:300])
+        n_dev += n > 0
+    assert n_dev > 0 and n_dev >= n_host or setup.tag.startswith("rep")
+    # the inputs apply to one submit only
+    setup.mapper.map_batch(seqs[:20], setup.e, setup.a)
+    assert setup.mapper.last_sam is None
+
+
 def test_double_buffered_submit_matches_sync(setup):
     seqs = [r[1] for r in setup.reads]
     half = len(seqs) // 2
