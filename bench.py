@@ -60,6 +60,8 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="reads of the workload the CPU baseline maps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (default: --steps)")
+    ap.add_argument("--e2e-threads", type=int, default=0, help="host threads of the end-to-end leg (default: cores/ranks - 3)")
+    ap.add_argument("--e2e-batch", type=int, default=0, help="reads per GPU batch of the end-to-end leg (default: the engine's)")
     args = ap.parse_args()
     WORKLOAD.clear()
     WORKLOAD.update(WORKLOADS[args.workload])
@@ -275,7 +277,7 @@ def run_ours(args):
         return float(t.item())
 
     from fem_b200 import host
-    from fem_b200.api import Params, Result, Stats, _check, load_library
+    from fem_b200.api import Params, Result, SamInputs, Stats, _check, load_library
     w = WORKLOAD
     fa, idx, fq = ensure_data(args, rank, world, barrier)
     lib = load_library()
@@ -288,16 +290,22 @@ def run_ours(args):
     params, batch, res = Params(0, 0, w["e"], w["a"]), reads.as_batch(), Result()
 
     # ---- resident leg: `value` -----------------------------------------------------------------
+    # names and qualities too: the SAM text is built on the device (k_sam), as in the end-to-end run
+    sam_in = SamInputs(reads.c.names, C.cast(reads.c.name_off, C.c_void_p), reads.c.quals, C.cast(reads.c.has_qual, C.c_void_p))
+    _check(lib.femgpu_set_sam_inputs(ctx, 0, C.byref(sam_in)))
     _check(lib.femgpu_map_batch(ctx, C.byref(params), C.byref(batch), C.byref(res)))  # stages the reads in HBM
     stats = res.stats.as_tuple()
-    tot, st = C.c_float(0), (C.c_float * 5)()
+    sam_text_bytes = int(res.sam_off[n_reads]) if res.sam_off else 0
+    import numpy as np
+    sam_host_reads = int(np.ctypeslib.as_array(res.sam_host, shape=(n_reads,)).sum()) if res.sam_off else None
+    tot, st = C.c_float(0), (C.c_float * 6)()
     for _ in range(max(args.warmup, 3)):
         _check(lib.femgpu_rerun_resident(ctx, C.byref(tot), C.byref(st)))
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     wall0 = time.perf_counter()
-    dev_ms, stage_ms, launches = 0.0, [0.0] * 5, 0
+    dev_ms, stage_ms, launches = 0.0, [0.0] * 6, 0
     ms5, nl = (C.c_float * 6)(), C.c_uint32(0)
     for _ in range(args.steps):
         _check(lib.femgpu_rerun_resident(ctx, C.byref(tot), C.byref(st)))
@@ -316,17 +324,21 @@ def run_ours(args):
 
     # ---- end-to-end leg: the whole `FEM map` run through the C ABI, host buffers -----------------
     cores = cpu_cores()
-    threads = max(1, cores // world - 3)
+    threads = args.e2e_threads or max(1, cores // world - 3)
     out = ("/dev/shm" if os.path.isdir("/dev/shm") else args.data_dir) + "/fem_bench_r%d.sam" % rank
     e2e_steps = args.e2e_steps or args.steps
-    hm.map_file(fq, out, w["e"], w["a"], threads=threads)  # warm-up: pinned staging buffers, page cache
-    barrier()
-    e0 = time.perf_counter()
-    e2e_stats, tm = None, None
+    hm.map_file(fq, out, w["e"], w["a"], threads=threads, batch_reads=args.e2e_batch)  # warm-up: pinned staging buffers, page cache
+    # every step writes a new file (what a user's run does): removing the previous step's output is not timed
+    e2e_stats, tm, e2e_s = None, None, 0.0
     for _ in range(e2e_steps):
-        e2e_stats, tm = hm.map_file(fq, out, w["e"], w["a"], threads=threads)
+        if os.path.exists(out):
+            os.remove(out)
+        barrier()
+        e0 = time.perf_counter()
+        e2e_stats, tm = hm.map_file(fq, out, w["e"], w["a"], threads=threads, batch_reads=args.e2e_batch)
+        e2e_s += time.perf_counter() - e0
     barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - e0)
+    e2e_s = max_over_ranks(e2e_s)
     sam_bytes = os.path.getsize(out)
     os.remove(out)
     assert e2e_stats[:5] == stats[:5], (e2e_stats, stats)
@@ -334,7 +346,7 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel -----------------------------------------------------------
     hbm_peak, peak_src = load_peaks()
-    per = [m / args.steps for m in stage_ms]  # ms per step: seed, candidates, verify, compaction, traceback
+    per = [m / args.steps for m in stage_ms]  # ms per step: seed, candidates, verify, compaction, traceback, SAM text
     n_s = w["read_len"] - w["k"] + 1
     cols, n_cand, c_before, n_maps = [int(x) for x in work]
     algo = {"k_seed": 16.0 * n_s * n_reads + w["read_len"] * n_reads,          # two LUT words per q-gram and strand + the read
@@ -342,10 +354,12 @@ def run_ours(args):
             "k_verify": n_cand * ((w["read_len"] + 2 * w["e"] + 3) // 4) + 16.0 * n_maps,  # 2-bit window per candidate
             "k_compact": 16.0 * n_maps + 4.0 * n_cand,
             "k_trace": n_maps * (2.0 * ((w["read_len"] + 2 * w["e"] + 3) // 4) + w["read_len"] + 40.0)}  # window twice, read, 40-byte record
-    names = ["k_seed", "k_cand", "k_verify", "k_compact", "k_trace"]
+    # text written + what it is built from (read, qualities, name, 16-byte mapping, 88-byte alignment record)
+    algo["k_sam"] = sam_text_bytes + 2.0 * w["read_len"] * stats[1] + 104.0 * n_maps
+    names = ["k_seed", "k_cand", "k_verify", "k_compact", "k_trace", "k_sam"]
     kernels = {n: {"ms": per[i], "algorithmic_bytes": algo[n], "gbs": algo[n] / (per[i] * 1e-3) / 1e9 if per[i] > 0 else None}
                for i, n in enumerate(names)}
-    top = max(range(5), key=lambda i: per[i])
+    top = max(range(len(names)), key=lambda i: per[i])
     ach = kernels[names[top]]["gbs"]
     traffic, traffic_src = None, None
     try:  # DRAM bytes of that kernel per launch, from the committed ncu --set full capture of this workload
@@ -377,7 +391,8 @@ def run_ours(args):
                     "phases_s": {k: tm[k] for k in ("wall", "parse", "gpu_wait", "format", "write")},
                     "what": "femhost_map_file: FASTQ parse -> pinned H2D -> kernels -> D2H -> mapping order, traceback, SAM text -> file on tmpfs"},
             "gpu_launches": launches, "roofline": roofline, "kernels": kernels, "roofline_verify_int32": verify_int32,
-            "stats": dict(zip(("reads", "mapped_reads", "candidates_before_filter", "candidates", "mappings", "infeasible"), stats))}
+            "stats": dict(zip(("reads", "mapped_reads", "candidates_before_filter", "candidates", "mappings", "infeasible"), stats)),
+            "device_sam": {"text_bytes": sam_text_bytes, "reads_left_to_host": sam_host_reads}}
 
     # ---- CPU baseline beside it (rank 0, N=1 only) ---------------------------------------------------
     if world == 1 and not args.no_cpu_baseline and os.access(REF_HDR, os.X_OK):

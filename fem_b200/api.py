@@ -62,7 +62,8 @@ class Result(C.Structure):
 
 
 class SamInputs(C.Structure):
-    _fields_ = [("names", C.c_void_p), ("name_off", C.c_void_p), ("quals", C.c_void_p), ("has_qual", C.c_void_p)]
+    _fields_ = [("names", C.c_void_p), ("name_off", C.c_void_p), ("quals", C.c_void_p), ("has_qual", C.c_void_p),
+                ("text_out", C.c_void_p), ("text_cap", C.c_uint64), ("off_out", C.c_void_p), ("host_out", C.c_void_p)]
 
 
 class Candidates(C.Structure):
@@ -99,7 +100,7 @@ EXPORTS = {
     "femgpu_free_pinned": (None, [C.c_void_p]),
     "femgpu_measure_int32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double * 3)]),
     "femgpu_last_work": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64 * 4)]),
-    "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 5)]),
+    "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 6)]),
 }
 
 _lib = None
@@ -324,6 +325,6 @@ class Mapper:
 
     def rerun_resident(self):
         tot = C.c_float(0)
-        st = (C.c_float * 5)()
+        st = (C.c_float * 6)()
         _check(self.lib.femgpu_rerun_resident(self.h, C.byref(tot), C.byref(st)))
         return tot.value, list(st)

@@ -85,7 +85,7 @@ static int run_sam(femgpu_ctx *c, Slot &s) {
   a.n_flagged = &dc->sam_flagged;
   a.text = nullptr;
   const unsigned grid = (n + 127) / 128;
-  k_sam<false><<<grid, 128, 0, s.stream>>>(a);
+  k_sam_len<<<grid, 128, 0, s.stream>>>(a);
   k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>());
   k_scan_blocks<<<1, 32, 0, s.stream>>>(s.sam_blocks.as<uint64_t>(), n_blocks, (uint64_t *)&dc->sam_total);
   k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>(),
@@ -99,7 +99,12 @@ static int run_sam(femgpu_ctx *c, Slot &s) {
   if (s.sam_total) {
     TRY(s.sam_text.reserve(s.sam_total + 16));
     a.text = s.sam_text.as<char>();
-    k_sam<true><<<grid, 128, 0, s.stream>>>(a);
+    // per-warp image: 1.25 x the mean span of 32 reads (more resident warps than with the maximum);
+    // the spans that do not fit are written byte-wise
+    uint64_t image = (s.sam_total / n + 1) * 40 + 256;
+    image = std::min<uint64_t>(std::max<uint64_t>((image + 15) & ~15ull, 2048), SAM_IMAGE_MAX);
+    CU(cudaFuncSetAttribute(k_sam_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * SAM_IMAGE_MAX)));
+    k_sam_write<<<grid, 128, 4 * image, s.stream>>>(a, (uint32_t)image);
     ++s.n_launches;
     CU(cudaGetLastError());
   }
@@ -123,13 +128,17 @@ static int fetch_result(Slot &s, femgpu_result *r) {
         CU(cudaMemcpyAsync(s.h_aln.p, s.aln.p, s.n_maps * sizeof(femgpu_alignment), cudaMemcpyDeviceToHost, s.stream));
       }
     }
-    if (s.sam_on) {
-      TRY(s.h_sam_off.reserve((n + 1ull) * 8));
-      TRY(s.h_sam_host.reserve(n + 16ull));
-      TRY(s.h_sam_text.reserve(s.sam_total + 16));
-      CU(cudaMemcpyAsync(s.h_sam_off.p, s.sam_off.p, (n + 1ull) * 8, cudaMemcpyDeviceToHost, s.stream));
-      CU(cudaMemcpyAsync(s.h_sam_host.p, s.sam_host.p, n, cudaMemcpyDeviceToHost, s.stream));
-      if (s.sam_total) CU(cudaMemcpyAsync(s.h_sam_text.p, s.sam_text.p, s.sam_total, cudaMemcpyDeviceToHost, s.stream));
+    if (s.sam_on) { // into the caller's buffers where it gave some (femgpu_sam_inputs)
+      const femgpu_sam_inputs &in = s.sam_in;
+      s.r_sam_off = in.off_out;
+      s.r_sam_host = in.host_out;
+      s.r_sam_text = in.text_out && s.sam_total <= in.text_cap ? in.text_out : nullptr;
+      if (!s.r_sam_off) { TRY(s.h_sam_off.reserve((n + 1ull) * 8)); s.r_sam_off = s.h_sam_off.as<uint64_t>(); }
+      if (!s.r_sam_host) { TRY(s.h_sam_host.reserve(n + 16ull)); s.r_sam_host = s.h_sam_host.as<uint8_t>(); }
+      if (!s.r_sam_text) { TRY(s.h_sam_text.reserve(s.sam_total + 16)); s.r_sam_text = s.h_sam_text.as<char>(); }
+      CU(cudaMemcpyAsync(s.r_sam_off, s.sam_off.p, (n + 1ull) * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaMemcpyAsync(s.r_sam_host, s.sam_host.p, n, cudaMemcpyDeviceToHost, s.stream));
+      if (s.sam_total) CU(cudaMemcpyAsync(s.r_sam_text, s.sam_text.p, s.sam_total, cudaMemcpyDeviceToHost, s.stream));
     }
     // infeasible read-strands are rare; count them from the status bytes
     TRY(s.h_status.reserve(2ull * n));
@@ -158,9 +167,9 @@ static int fetch_result(Slot &s, femgpu_result *r) {
     r->alns = s.has_aln && s.n_maps ? s.h_aln.as<femgpu_alignment>() : nullptr;
     r->stats = s.stats;
     const bool sam = s.sam_on && n > 0;
-    r->sam_text = sam ? s.h_sam_text.as<char>() : nullptr;
-    r->sam_off = sam ? s.h_sam_off.as<uint64_t>() : nullptr;
-    r->sam_host = sam ? s.h_sam_host.as<uint8_t>() : nullptr;
+    r->sam_text = sam ? s.r_sam_text : nullptr;
+    r->sam_off = sam ? s.r_sam_off : nullptr;
+    r->sam_host = sam ? s.r_sam_host : nullptr;
   }
   return 0;
 }
@@ -297,7 +306,7 @@ extern "C" int femgpu_last_work(femgpu_ctx *c, uint64_t work[4]) {
   return 0;
 }
 
-extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[5]) {
+extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_stage[6]) {
   if (!c) return set_error(FEMGPU_EINVAL, "null context");
   Slot &s = c->slot[c->last_slot];
   if (s.busy) return set_error(FEMGPU_ESTATE, "slot busy");
@@ -307,14 +316,17 @@ extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_st
   cudaEventRecord(s.ev[0], s.stream);
   TRY(run_seed_and_candidates(c, s, pl));
   TRY(run_verify_and_compact(c, s, pl));
+  TRY(run_sam(c, s)); // the batch's names and qualities are still resident when it was submitted with SAM inputs
+  cudaEventRecord(s.ev[7], s.stream);
   CU(cudaStreamSynchronize(s.stream));
   float t;
   if (ms_stage)
   {
     for (int i = 0; i < 4; ++i) { cudaEventElapsedTime(&t, s.ev[i], s.ev[i + 1]); ms_stage[i] = t; }
     cudaEventElapsedTime(&t, s.ev[4], s.ev[6]); ms_stage[4] = t;
+    cudaEventElapsedTime(&t, s.ev[6], s.ev[7]); ms_stage[5] = t;
   }
-  cudaEventElapsedTime(&t, s.ev[0], s.ev[6]);
+  cudaEventElapsedTime(&t, s.ev[0], s.ev[7]);
   if (ms_total) *ms_total = t;
   return 0;
 }

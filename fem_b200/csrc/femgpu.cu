@@ -133,6 +133,9 @@ struct Slot {
   bool busy = false;
   bool has_aln = false;
   uint64_t sam_flagged = 0;
+  char *r_sam_text = nullptr;     // where this batch's SAM text went on the host (caller's or ours)
+  uint64_t *r_sam_off = nullptr;
+  uint8_t *r_sam_host = nullptr;
   femgpu_params params{};
   uint32_t n_reads = 0;
   uint64_t n_bases = 0;

@@ -9,11 +9,13 @@
 //     QNAME FLAG RNAME POS 255 CIGAR * 0 0 SEQ QUAL NM:i MD:Z, the first record primary with SEQ/QUAL in
 //     the file's orientation, the others flag | 256 with "*".
 // Start, CIGAR and MD come from k_trace; reads with an alignment k_trace left to the host
-// (FEMGPU_ALN_HOST) are left to the host here as well.  Two passes of the same emitter: lengths (then
-// an exclusive scan over reads), text.
+// (FEMGPU_ALN_HOST) are left to the host here as well.  Two passes of the same emitter: lengths
+// (k_sam_len, then an exclusive scan over reads), text (k_sam_write).
 #pragma once
 #include "common.cuh"
 #include "k_trace.cuh"
+
+#define SAM_IMAGE_MAX 24576u // most bytes of shared memory per warp in k_sam_write (four warps per block)
 
 struct SamArgs {
   const char *bases;          // the batch's reads as uploaded (file orientation)
@@ -40,41 +42,31 @@ __device__ __forceinline__ uint64_t sam_key(const ulonglong2 &m) { // src/align.
   return (dist << 60) | (dir << 59) | (m.x + (uint64_t)(int64_t)(int32_t)(uint32_t)m.y);
 }
 
-template <bool WRITE>
+// MODE 0: lengths only; 1: every byte to p; 2: every byte but the primary record's SEQ and QUAL, whose
+// room is left free and whose position is returned (the warp copies them, k_sam_write)
+template <int MODE>
 struct SamOut {
   char *p;
   uint32_t n;
-  __device__ __forceinline__ void ch(char c) { if (WRITE) p[n] = c; ++n; }
+  __device__ __forceinline__ void ch(char c) { if (MODE) p[n] = c; ++n; }
   __device__ __forceinline__ void mem(const char *s, uint32_t len) {
-    if (WRITE) for (uint32_t i = 0; i < len; ++i) p[n + i] = s[i];
+    if (MODE) for (uint32_t i = 0; i < len; ++i) p[n + i] = s[i];
     n += len;
   }
   __device__ __forceinline__ void lit(const char *s) { while (*s) ch(*s++); }
-  __device__ __forceinline__ void num(uint64_t v) {
-    char tmp[20];
-    int k = 0;
-    do { tmp[k++] = (char)('0' + (int)(v % 10u)); v /= 10u; } while (v);
-    while (k) ch(tmp[--k]);
+  __device__ __forceinline__ void num(uint32_t v) { // every number of a record fits 32 bits (positions are < 2^31)
+    uint32_t digits = 1;
+    for (uint32_t t = v; t >= 10u; t /= 10u) ++digits;
+    if (MODE) for (uint32_t k = digits, t = v; k--; t /= 10u) p[n + k] = (char)('0' + t % 10u);
+    n += digits;
   }
 };
 
-template <bool WRITE>
-__global__ void __launch_bounds__(128) k_sam(SamArgs A) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.n_reads) return;
-  const uint64_t m0 = A.rs_map_first[2ull * i], m1 = A.rs_map_first[2ull * i + 2];
-  const uint32_t n = (uint32_t)(m1 - m0);
-  if (!WRITE) { A.read_bytes[i] = 0; A.host_flag[i] = 0; }
-  if (n == 0) return;
-  if (WRITE && A.host_flag[i]) return;
-  if (!WRITE) {
-    bool host = n > 64;
-    for (uint32_t j = 0; j < n && !host; ++j) {
-      const uint32_t w0 = A.aln[(m0 + j) * ALN_WORDS];
-      host = ((w0 >> 16) & 0xFFu) == ALN_HOST || (w0 >> 24) == ALN_HOST;
-    }
-    if (host) { A.host_flag[i] = 1; atomicAdd(A.n_flagged, 1ull); return; }
-  }
+// the records of read i (n >= 1 mappings, not left to the host); returns the bytes.  seq_at: MODE 2,
+// offset of SEQ within the text; with_qual: MODE 2, QUAL follows SEQ + tab (else '*' was written)
+template <int MODE>
+__device__ __forceinline__ uint32_t sam_emit_read(const SamArgs &A, uint32_t i, uint64_t m0, uint32_t n, char *p,
+                                                  uint32_t *seq_at, bool *with_qual) {
   // mapping order: stable by key (n <= 64)
   uint8_t ord[64];
   if (n == 1) ord[0] = 0;
@@ -93,8 +85,8 @@ __global__ void __launch_bounds__(128) k_sam(SamArgs A) {
   const char *name = A.names + A.name_off[i];
   uint32_t name_l = 0;
   while (name[name_l]) ++name_l;
-  SamOut<WRITE> o;
-  o.p = WRITE ? A.text + A.text_off[i] : nullptr;
+  SamOut<MODE> o;
+  o.p = p;
   o.n = 0;
   for (uint32_t mi = 0; mi < n; ++mi) {
     const uint64_t m = m0 + ord[mi];
@@ -111,7 +103,7 @@ __global__ void __launch_bounds__(128) k_sam(SamArgs A) {
     o.ch('\t');
     o.mem(A.rnames + A.rname_off[r], A.rname_off[r + 1] - A.rname_off[r]);
     o.ch('\t');
-    o.num((uint64_t)pos + 1);
+    o.num(pos + 1u);
     o.lit("\t255\t");
     if (n_cigar == 0) o.ch('*');
     for (uint32_t ci = 0; ci < n_cigar; ++ci) {
@@ -121,19 +113,118 @@ __global__ void __launch_bounds__(128) k_sam(SamArgs A) {
     }
     o.lit("\t*\t0\t0\t");
     if (mi == 0) { // the primary record carries SEQ/QUAL in the file's orientation (src/align.c:79,87)
-      o.mem(A.bases + off, l); // canonical reads only (others are left to the host): printed as they are
-      o.ch('\t');
-      if (!A.has_qual[i] || A.quals[off] == ' ') o.ch('*'); // htslib sam.c:3047
-      else o.mem(A.quals + off, l);
+      const bool q = A.has_qual[i] && A.quals[off] != ' '; // htslib sam.c:3047 prints '*' otherwise
+      if (MODE == 2) {
+        *seq_at = o.n;
+        *with_qual = q;
+        o.n += l;
+        o.ch('\t');
+        if (q) o.n += l;
+        else o.ch('*');
+      } else {
+        o.mem(A.bases + off, l); // canonical reads only (others are left to the host): printed as they are
+        o.ch('\t');
+        if (q) o.mem(A.quals + off, l);
+        else o.ch('*');
+      }
     } else {
       o.lit("*\t*");
     }
     o.lit("\tNM:i:");
     o.num(dist);
     o.lit("\tMD:Z:");
-    if (WRITE) for (uint32_t k = 0; k < md_len; ++k) o.p[o.n + k] = (char)((al[10 + (k >> 2)] >> (8 * (k & 3))) & 0xFFu);
+    if (MODE) for (uint32_t k = 0; k < md_len; ++k) o.p[o.n + k] = (char)((al[10 + (k >> 2)] >> (8 * (k & 3))) & 0xFFu);
     o.n += md_len;
     o.ch('\n');
   }
-  if (!WRITE) A.read_bytes[i] = o.n;
+  return o.n;
+}
+
+// pass 1: bytes of every read's text, host flags
+__global__ void __launch_bounds__(128) k_sam_len(SamArgs A) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.n_reads) return;
+  const uint64_t m0 = A.rs_map_first[2ull * i], m1 = A.rs_map_first[2ull * i + 2];
+  const uint32_t n = (uint32_t)(m1 - m0);
+  A.read_bytes[i] = 0;
+  A.host_flag[i] = 0;
+  if (n == 0) return;
+  bool host = n > 64;
+  for (uint32_t j = 0; j < n && !host; ++j) {
+    const uint32_t w0 = A.aln[(m0 + j) * ALN_WORDS];
+    host = ((w0 >> 16) & 0xFFu) == ALN_HOST || (w0 >> 24) == ALN_HOST;
+  }
+  if (host) { A.host_flag[i] = 1; atomicAdd(A.n_flagged, 1ull); return; }
+  A.read_bytes[i] = sam_emit_read<0>(A, i, m0, n, nullptr, nullptr, nullptr);
+}
+
+// len bytes of src[at..] into shared memory, by the warp: each lane takes four bytes out of two aligned
+// words (the buffers are padded past their last byte, slot_reserve)
+__device__ __forceinline__ void sam_copy_field(char *dst, const char *src, uint64_t at, uint32_t len, uint32_t lane) {
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(src + (at & ~3ull));
+  const uint32_t sh = (uint32_t)(at & 3u) * 8u;
+  for (uint32_t k = lane * 4u; k < len; k += 128u) {
+    const uint32_t v = __funnelshift_r(w[k >> 2], w[(k >> 2) + 1], sh);
+    dst[k] = (char)v;
+    if (k + 1 < len) dst[k + 1] = (char)(v >> 8);
+    if (k + 2 < len) dst[k + 2] = (char)(v >> 16);
+    if (k + 3 < len) dst[k + 3] = (char)(v >> 24);
+  }
+}
+
+// pass 2: the text.  The 32 reads of a warp own one contiguous span of the output (text_off is the scan
+// of their sizes): each lane builds its read's records in the warp's shared-memory image of that span,
+// the warp copies SEQ and QUAL of each read into it with coalesced loads, and the image goes out as
+// 16-byte stores (the image starts at the span's offset within its 16-byte line, so both sides are
+// aligned alike).  Spans larger than `image` bytes are written byte-wise straight to global memory.
+__global__ void __launch_bounds__(128) k_sam_write(SamArgs A, uint32_t image) {
+  extern __shared__ __align__(16) char sam_smem[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, i0 = i - lane;
+  if (i0 >= A.n_reads) return;
+  const uint32_t i1 = min(i0 + 32u, A.n_reads);
+  const uint64_t t0 = A.text_off[i0], t1 = A.text_off[i1];
+  if (t1 == t0) return;
+  const bool live = i < A.n_reads;
+  uint64_t m0 = 0;
+  uint32_t n = 0;
+  if (live && !A.host_flag[i]) {
+    m0 = A.rs_map_first[2ull * i];
+    n = (uint32_t)(A.rs_map_first[2ull * i + 2] - m0);
+  }
+  const uint32_t skew = (uint32_t)(t0 & 15u);
+  const uint64_t total = (t1 - t0) + skew;
+  if (total > image) {
+    if (n) sam_emit_read<1>(A, i, m0, n, A.text + A.text_off[i], nullptr, nullptr);
+    return;
+  }
+  char *img = sam_smem + (size_t)warp * image;
+  uint32_t seq_at = 0xFFFFFFFFu, l = 0;
+  uint64_t roff = 0;
+  bool with_qual = false;
+  if (n) {
+    const uint32_t mine = (uint32_t)(A.text_off[i] - t0) + skew;
+    sam_emit_read<2>(A, i, m0, n, img + mine, &seq_at, &with_qual);
+    seq_at += mine;
+    roff = A.read_off[i];
+    l = (uint32_t)(A.read_off[i + 1] - roff);
+  }
+  __syncwarp();
+  for (uint32_t r = 0; r < 32u; ++r) {
+    const uint32_t sp = __shfl_sync(0xFFFFFFFFu, seq_at, r);
+    if (sp == 0xFFFFFFFFu) continue;
+    const uint32_t rl = __shfl_sync(0xFFFFFFFFu, l, r);
+    const uint64_t ro = __shfl_sync(0xFFFFFFFFu, roff, r);
+    const bool wq = __shfl_sync(0xFFFFFFFFu, (int)with_qual, r) != 0;
+    sam_copy_field(img + sp, A.bases, ro, rl, lane);
+    if (wq) sam_copy_field(img + sp + rl + 1, A.quals, ro, rl, lane);
+  }
+  __syncwarp();
+  char *dst = A.text + (t0 - skew); // 16-byte aligned (the text buffer is)
+  const uint32_t tot = (uint32_t)total;
+  for (uint32_t c = lane * 16u; c < tot; c += 512u) {
+    if (c >= skew && c + 16u <= tot) *reinterpret_cast<uint4 *>(dst + c) = *reinterpret_cast<const uint4 *>(img + c);
+    else
+      for (uint32_t k = max(c, skew); k < min(c + 16u, tot); ++k) dst[k] = img[k];
+  }
 }

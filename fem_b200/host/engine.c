@@ -9,6 +9,7 @@
  *   writer thread      batches in file order -> output: byte-identical to the reference's -t 1
  */
 #include <fcntl.h>
+#include <inttypes.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -20,6 +21,11 @@
 
 #include "femhost.h"
 #include "host_internal.h"
+
+/* reads per GPU batch: small enough that the first SAM text is on its way a few milliseconds into the
+ * run and the last batch's tail is short, large enough to fill the device (measured on cfg2: 65536
+ * beats 131072 by 10-20 %, 262144 loses 30 %) */
+#define DEFAULT_BATCH_READS 65536u
 
 /* ---- blocking FIFO of pointers ---------------------------------------------------------------- */
 typedef struct {
@@ -193,6 +199,7 @@ struct batch {
   uint64_t *sam_off;        /* n_reads + 1 */
   uint8_t *sam_host;        /* n_reads: 1 = this read is formatted here */
   int has_sam;
+  double t_trace[6];        /* FEM_TRACE: parsed, gpu start, gpu end, text ready, offsets assigned, written */
   uint64_t sam_dev_reads;   /* mapped reads of the batch the device formatted */
   size_t cap_sam_text, cap_sam_reads;
   size_t cap_first, cap_maps, cap_alns;
@@ -216,7 +223,7 @@ static void pool_free(femhost_mapper *m) {
     free(b->first);
     free(b->maps);
     free(b->alns);
-    free(b->sam_text); free(b->sam_off); free(b->sam_host);
+    femgpu_free_pinned(b->sam_text); femgpu_free_pinned(b->sam_off); femgpu_free_pinned(b->sam_host);
     for (size_t c = 0; c < b->cap_chunks; ++c) femhost_str_free(&b->text[c]);
     free(b->text);
     free(b->items);
@@ -233,13 +240,15 @@ typedef struct {
   int out_fd;               /* -1: build the text, write nothing */
   int out_seekable;         /* regular file: chunks are written in parallel with pwrite */
   uint64_t out_off;         /* next file offset (writer thread only) */
+  int trace;                /* FEM_TRACE=1: one line per batch with its times on stderr */
+  double t_start, t_enter;
   int device_sam;           /* SAM text formatted by k_sam (FEM_DEVICE_SAM=0: on the host) */
   int out_populate;         /* madvise(MADV_POPULATE_WRITE) before the copy (FEM_SAM_POPULATE=0 turns it off) */
   int out_mmap;             /* tmpfs: chunks are copied into a shared mapping (pwrite holds the inode lock) */
   uint64_t out_alloc;       /* size the file has been extended to (writer thread only) */
   int writes_outstanding;   /* guarded by mu; writer waits for 0 before the file is closed */
   pthread_cond_t writes_done;
-  fifo q_free, q_parsed, q_work;
+  fifo q_free, q_parsed, q_work, q_write;
   /* finished batches wait here for the writer, indexed by seq % n_batches */
   batch **done;
   size_t n_batches;
@@ -270,7 +279,7 @@ static void run_fail(run_state *r, const char *msg) {
 
 static void *reader_main(void *arg) {
   run_state *r = (run_state *)arg;
-  const uint32_t per_batch = r->opt->batch_reads ? r->opt->batch_reads : 131072u;
+  const uint32_t per_batch = r->opt->batch_reads ? r->opt->batch_reads : DEFAULT_BATCH_READS;
   uint64_t to_skip = r->opt->skip_reads, left = r->opt->max_reads ? r->opt->max_reads : UINT64_MAX, seq = 0;
   double busy = 0;
   batch *b = NULL;
@@ -287,6 +296,7 @@ static void *reader_main(void *arg) {
     if (to_skip) { to_skip -= (uint64_t)n; continue; } /* another shard's reads: parsed and dropped */
     left -= (uint64_t)n;
     b->seq = seq++;
+    b->t_trace[0] = femhost_now();
     fifo_push(&r->q_parsed, b);
     b = NULL;
   }
@@ -347,6 +357,7 @@ static void *par_reader_main(void *arg) {
       else rc = femhost_parse_fastq4(raw, raw + n, &b->reads);
     }
     pa->busy += femhost_now() - t0;
+    b->t_trace[0] = femhost_now();
     b->seq = i;
     if (rc) {
       pthread_mutex_lock(&r->mu);
@@ -376,8 +387,25 @@ typedef struct {
   double busy;
 } gpu_arg;
 
+/* pinned room of a batch for the device's SAM text (text_bytes) or offsets + flags (n_off); contents are not kept */
+static void batch_sam_room(batch *b, size_t text_bytes, size_t n_off) {
+  if (text_bytes) {
+    femgpu_free_pinned(b->sam_text);
+    b->sam_text = (char *)femgpu_alloc_pinned(text_bytes);
+    b->cap_sam_text = b->sam_text ? text_bytes : 0;
+  }
+  if (n_off) {
+    femgpu_free_pinned(b->sam_off);
+    femgpu_free_pinned(b->sam_host);
+    b->sam_off = (uint64_t *)femgpu_alloc_pinned(n_off * 8);
+    b->sam_host = (uint8_t *)femgpu_alloc_pinned(n_off);
+    b->cap_sam_reads = b->sam_off && b->sam_host ? n_off : 0;
+  }
+}
+
 /* marks a batch complete for the writer */
 static void batch_finished(run_state *r, batch *b) {
+  b->t_trace[3] = femhost_now();
   pthread_mutex_lock(&r->mu);
   r->done[b->seq % r->n_batches] = b;
   pthread_cond_broadcast(&r->batch_done);
@@ -396,12 +424,20 @@ static void *gpu_main(void *arg) {
     int ok = !r->failed && !r->restart_sequential;
     if (ok) {
       const double t0 = femhost_now();
+      b->t_trace[1] = t0;
       femgpu_batch gb = {b->reads.bases, b->reads.base_off, n};
       femgpu_result res;
       int rc = 0;
       if (r->device_sam && n && b->reads.quals && b->reads.has_qual) {
-        femgpu_sam_inputs si = {b->reads.names, b->reads.name_off, b->reads.quals, b->reads.has_qual};
-        rc = femgpu_set_sam_inputs(ctx, ga->slot, &si);
+        /* the text comes back into pinned buffers of the batch: one record per read is the first guess,
+         * a batch that needs more lands in the library's buffer once and the room grows */
+        const uint64_t guess = 2 * b->reads.n_bases + b->reads.name_off[n] + 160ull * n;
+        if (guess > b->cap_sam_text) batch_sam_room(b, guess + guess / 4, 0);
+        if ((size_t)n + 1 > b->cap_sam_reads) batch_sam_room(b, 0, (size_t)n + 1);
+        femgpu_sam_inputs si = {b->reads.names, b->reads.name_off, b->reads.quals, b->reads.has_qual,
+                                b->sam_text, b->sam_text ? b->cap_sam_text : 0, b->sam_off, b->sam_host};
+        if (!b->sam_off || !b->sam_host) rc = femhost_set_error(-3, "out of pinned memory for the SAM offsets");
+        else rc = femgpu_set_sam_inputs(ctx, ga->slot, &si);
       }
       if (!rc) rc = femgpu_submit_batch(ctx, ga->slot, &r->opt->params, &gb);
       if (!rc) rc = femgpu_wait_batch(ctx, ga->slot, &res);
@@ -420,15 +456,13 @@ static void *gpu_main(void *arg) {
         b->has_sam = res.sam_off != NULL;
         if (b->has_sam) {
           const uint64_t nb = res.sam_off[n];
-          if ((size_t)n + 1 > b->cap_sam_reads) {
-            b->cap_sam_reads = (size_t)n + 1;
-            b->sam_off = (uint64_t *)realloc(b->sam_off, b->cap_sam_reads * 8);
-            b->sam_host = (uint8_t *)realloc(b->sam_host, b->cap_sam_reads);
+          if (res.sam_text != b->sam_text && nb) { /* did not fit: copy out of the slot's buffer, more room next time */
+            batch_sam_room(b, nb + nb / 4 + 4096, 0);
+            if (!b->sam_text) { run_fail(r, "out of pinned memory for the SAM text"); b->has_sam = 0; }
+            else memcpy(b->sam_text, res.sam_text, nb);
           }
-          if (nb > b->cap_sam_text) { b->cap_sam_text = nb + nb / 8 + 4096; b->sam_text = (char *)realloc(b->sam_text, b->cap_sam_text); }
-          memcpy(b->sam_off, res.sam_off, ((size_t)n + 1) * 8);
-          memcpy(b->sam_host, res.sam_host, n);
-          memcpy(b->sam_text, res.sam_text, nb);
+        }
+        if (b->has_sam) {
           b->sam_dev_reads = 0;
           for (uint32_t i = 0; i < n; ++i) b->sam_dev_reads += b->sam_off[i + 1] > b->sam_off[i];
         }
@@ -436,7 +470,8 @@ static void *gpu_main(void *arg) {
         float ms[6];
         femgpu_last_timings(ctx, ms, &b->n_launches);
       }
-      ga->busy += femhost_now() - t0;
+      b->t_trace[2] = femhost_now();
+      ga->busy += b->t_trace[2] - t0;
     }
     if (!ok) { batch_finished(r, b); continue; }
     /* hand the batch to the SAM workers, CHUNK_READS reads at a time */
@@ -448,22 +483,33 @@ static void *gpu_main(void *arg) {
       b->cap_chunks = n_chunks;
     }
     b->n_chunks = n_chunks;
-    b->chunks_left = (int)n_chunks;
-    if (n_chunks == 0) { batch_finished(r, b); continue; }
+    /* chunks the device formatted completely are ready as they are; the others go to the workers */
+    int to_format = 0;
     for (uint32_t c = 0; c < n_chunks; ++c) {
-      b->items[c].b = b;
-      b->items[c].chunk = c;
-      b->items[c].write = 0;
-      b->items[c].ext = NULL;
-      b->items[c].ext_len = 0;
-      fifo_push(&r->q_work, &b->items[c]);
+      work_item *it = &b->items[c];
+      const uint32_t lo = c * CHUNK_READS, hi = lo + CHUNK_READS < n ? lo + CHUNK_READS : n;
+      it->b = b;
+      it->chunk = c;
+      it->write = 0;
+      it->ext = NULL;
+      it->ext_len = 0;
+      if (b->has_sam && !memchr(b->sam_host + lo, 1, hi - lo)) {
+        it->ext = b->sam_text + b->sam_off[lo];
+        it->ext_len = (size_t)(b->sam_off[hi] - b->sam_off[lo]);
+        b->text[c].l = 0;
+      } else ++to_format;
     }
+    b->chunks_left = to_format;
+    if (to_format == 0) { batch_finished(r, b); continue; }
+    for (uint32_t c = 0; c < n_chunks; ++c)
+      if (!b->items[c].ext) fifo_push(&r->q_work, &b->items[c]);
   }
   return NULL;
 }
 
 typedef struct {
   run_state *r;
+  fifo *q;                  /* q_work: SAM text of chunks; q_write: copies into the output file */
   double busy, busy_write;
 } worker_arg;
 
@@ -483,7 +529,7 @@ static void *worker_main(void *arg) {
   const int e = r->opt->params.e;
   static const char no_qual[2] = {' ', 0}; /* prints as '*' (htslib sam.c:3047) */
   work_item *it;
-  while ((it = (work_item *)fifo_pop(&r->q_work)) != NULL) {
+  while ((it = (work_item *)fifo_pop(wa->q)) != NULL) {
     const double t0 = femhost_now();
     batch *b = it->b;
     femhost_str *out = &b->text[it->chunk];
@@ -506,6 +552,10 @@ static void *worker_main(void *arg) {
       pthread_mutex_unlock(&r->mu);
       if (left == 0 && b->map_base) { munmap(b->map_base, b->map_len); b->map_base = NULL; }
       wa->busy_write += femhost_now() - t0;
+      if (left == 0 && r->trace)
+        fprintf(stderr, "[trace] batch %" PRIu64 " (%u reads): parsed %.1f, gpu %.1f-%.1f, text %.1f, offsets %.1f, written %.1f ms\n", b->seq,
+                b->reads.n_records, 1e3 * (b->t_trace[0] - r->t_start), 1e3 * (b->t_trace[1] - r->t_start), 1e3 * (b->t_trace[2] - r->t_start),
+                1e3 * (b->t_trace[3] - r->t_start), 1e3 * (b->t_trace[4] - r->t_start), 1e3 * (femhost_now() - r->t_start));
       pthread_mutex_lock(&r->mu);
       if (--r->writes_outstanding == 0) pthread_cond_broadcast(&r->writes_done);
       pthread_mutex_unlock(&r->mu);
@@ -515,11 +565,6 @@ static void *worker_main(void *arg) {
     out->l = 0;
     const uint32_t lo = it->chunk * CHUNK_READS;
     const uint32_t hi = lo + CHUNK_READS < b->reads.n_records ? lo + CHUNK_READS : b->reads.n_records;
-    if (b->has_sam && !memchr(b->sam_host + lo, 1, hi - lo)) { /* the device formatted every read of the chunk */
-      it->ext = b->sam_text + b->sam_off[lo];
-      it->ext_len = (size_t)(b->sam_off[hi] - b->sam_off[lo]);
-      goto chunk_done;
-    }
     for (uint32_t i = lo; i < hi && !r->failed; ++i) {
       const size_t n = (size_t)(b->first[i + 1] - b->first[i]);
       if (!n) continue;
@@ -536,7 +581,6 @@ static void *worker_main(void *arg) {
                            b->maps + b->first[i], b->has_alns ? b->alns + b->first[i] : NULL, n, out))
         run_fail(r, femhost_last_error());
     }
-  chunk_done:
     wa->busy += femhost_now() - t0;
     pthread_mutex_lock(&r->mu);
     const int left = --b->chunks_left;
@@ -592,13 +636,14 @@ static void *writer_main(void *arg) {
         if (mp != MAP_FAILED) { b->map_base = (char *)mp; b->map_len = (size_t)(hi - m0); b->map_file_off = m0; }
       }
     }
+    b->t_trace[4] = femhost_now();
     if (n_writes) { /* hand the copies to the workers; the last one recycles the batch */
       pthread_mutex_lock(&r->mu);
       b->writes_left = n_writes;
       r->writes_outstanding += n_writes;
       pthread_mutex_unlock(&r->mu);
       for (uint32_t c = 0; c < b->n_chunks; ++c)
-        if (b->items[c].write) fifo_push(&r->q_work, &b->items[c]);
+        if (b->items[c].write) fifo_push(&r->q_write, &b->items[c]);
     }
     busy += femhost_now() - t0;
     r->stats.num_reads += b->stats.num_reads;
@@ -638,7 +683,10 @@ static int parallel_readable(const char *path, uint64_t *size) {
   return n == 2 && b[0] == '@';
 }
 
-#define N_PAR_READERS 3
+#define N_PAR_READERS 4
+/* threads that copy finished text into the output file: the page cache's per-file locks stop scaling
+ * beyond about six (measured on tmpfs: 7.5 GB/s from six threads, the same from sixteen at three times the CPU time) */
+#define MAX_COPIERS 6
 
 static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
                         int parallel, femgpu_stats *stats, femhost_map_timing *timing, int *restart) {
@@ -647,13 +695,14 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   r.m = m;
   r.opt = opt;
   r.fd = -1;
+  r.t_enter = femhost_now();
   if (parallel) {
     r.fd = open(reads_path, O_RDONLY);
     if (r.fd < 0) return femhost_set_error(-1, "Cannot find sequence file!");
     struct stat st;
     fstat(r.fd, &st);
     r.file_size = (uint64_t)st.st_size;
-    const uint64_t per_batch = opt->batch_reads ? opt->batch_reads : 131072u;
+    const uint64_t per_batch = opt->batch_reads ? opt->batch_reads : DEFAULT_BATCH_READS;
     r.chunk_bytes = per_batch * 224; /* about per_batch reads of 100 bp; only the batch granularity depends on it */
     if (r.chunk_bytes < 4096) r.chunk_bytes = 4096;
     r.n_chunks = (r.file_size + r.chunk_bytes - 1) / r.chunk_bytes;
@@ -682,8 +731,11 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   }
   pthread_cond_init(&r.writes_done, NULL);
   const double t_start = femhost_now();
-  const int n_gpu_threads = 2 * m->n_gpus, n_workers = opt->n_threads, n_readers = parallel ? N_PAR_READERS : 1;
-  r.n_batches = (size_t)(2 * n_gpu_threads + 2 + (parallel ? N_PAR_READERS : 0));
+  r.t_start = t_start;
+  r.trace = getenv("FEM_TRACE") && atoi(getenv("FEM_TRACE")) != 0;
+  const int n_gpu_threads = 2 * m->n_gpus, n_format = opt->n_threads, n_readers = parallel ? N_PAR_READERS : 1;
+  const int n_copiers = opt->n_threads < MAX_COPIERS ? opt->n_threads : MAX_COPIERS, n_workers = n_format + n_copiers;
+  r.n_batches = (size_t)(2 * n_gpu_threads + 6 + (parallel ? N_PAR_READERS : 0));
   if (m->n_pool != r.n_batches) {
     pool_free(m);
     m->pool = (batch *)calloc(r.n_batches, sizeof(batch));
@@ -695,6 +747,7 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   fifo_init(&r.q_free, r.n_batches + 1);
   fifo_init(&r.q_parsed, r.n_batches + 1);
   fifo_init(&r.q_work, 1 << 16);
+  fifo_init(&r.q_write, 1 << 16);
   pthread_mutex_init(&r.mu, NULL);
   pthread_cond_init(&r.batch_done, NULL);
   for (size_t i = 0; i < r.n_batches; ++i) fifo_push(&r.q_free, &pool[i]);
@@ -723,20 +776,23 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   }
   for (int i = 0; i < n_workers; ++i) {
     wa[i].r = &r;
+    wa[i].q = i < n_format ? &r.q_work : &r.q_write;
     pthread_create(&th_worker[i], NULL, worker_main, &wa[i]);
   }
   for (int i = 0; i < n_readers; ++i) { pthread_join(th_reader[i], NULL); if (parallel) r.tm.parse += pa[i].busy; }
   for (int i = 0; i < n_gpu_threads; ++i) { pthread_join(th_gpu[i], NULL); r.tm.gpu_wait += ga[i].busy; }
   pthread_join(th_writer, NULL); /* returns once every chunk is formatted, ordered and written */
   fifo_close(&r.q_work);
+  fifo_close(&r.q_write);
   for (int i = 0; i < n_workers; ++i) { pthread_join(th_worker[i], NULL); r.tm.format += wa[i].busy; r.tm.write += wa[i].busy_write; }
   if (r.out_fd >= 0 && close(r.out_fd) != 0) run_fail(&r, "closing the SAM file failed");
   pthread_cond_destroy(&r.writes_done);
   r.tm.wall = femhost_now() - t_start;
+  if (r.trace) fprintf(stderr, "[trace] entry to thread start %.1f ms, threads %.1f ms\n", 1e3 * (t_start - r.t_enter), 1e3 * r.tm.wall);
   if (r.rd) femhost_reader_close(r.rd);
   if (r.fd >= 0) close(r.fd);
   free(r.done); free(th_worker); free(wa);
-  fifo_destroy(&r.q_free); fifo_destroy(&r.q_parsed); fifo_destroy(&r.q_work);
+  fifo_destroy(&r.q_free); fifo_destroy(&r.q_parsed); fifo_destroy(&r.q_work); fifo_destroy(&r.q_write);
   pthread_mutex_destroy(&r.mu);
   pthread_cond_destroy(&r.batch_done);
   if (stats) *stats = r.stats;

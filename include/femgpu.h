@@ -115,6 +115,14 @@ typedef struct {
   const uint64_t *name_off; /* n_reads + 1 */
   const char *quals;
   const uint8_t *has_qual;  /* n_reads */
+  /* Optional (all NULL/0: the library's own buffers, valid until the slot's next submit): pinned host
+   * memory of the caller that femgpu_wait_batch copies the text, the n_reads + 1 offsets and the
+   * n_reads flags into, so that the result outlives the slot.  A text larger than text_cap lands in the
+   * library's buffer instead (result.sam_text != text_out tells). */
+  char *text_out;
+  uint64_t text_cap;
+  uint64_t *off_out;
+  uint8_t *host_out;
 } femgpu_sam_inputs;
 
 /* ---- life cycle ------------------------------------------------------------------------------ */
@@ -220,8 +228,9 @@ int femgpu_last_timings(femgpu_ctx *ctx, float ms[6], uint32_t *n_launches);
  * filter", src/filter.c:202), [3] mappings emitted. */
 int femgpu_last_work(femgpu_ctx *ctx, uint64_t work[4]);
 /* Run the device pipeline of the last submitted batch again with inputs already resident in HBM
- * (no H2D, no D2H of mappings); returns device milliseconds.  bench.py's `value`. */
-int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[5]);
+ * (no H2D, no D2H of mappings); returns device milliseconds.  bench.py's `value`.  ms_stage: seeds,
+ * candidates, verification, compaction, traceback, SAM text (0 unless the batch had SAM inputs). */
+int femgpu_rerun_resident(femgpu_ctx *ctx, float *ms_total, float ms_stage[6]);
 
 /* INT32 pipe peak of the device in 10^9 instructions per second, measured with dependency-chain
  * free kernels: [0] LOP3 (logic), [1] IADD3 (add), [2] shift+logic pairs as in the Myers column.
