@@ -8,6 +8,7 @@
  *   -t worker threads  per-read mapping order, traceback, SAM text, chunk by chunk (sam.c)
  *   writer thread      batches in file order -> output: byte-identical to the reference's -t 1
  */
+#define _GNU_SOURCE /* fallocate, MADV_POPULATE_WRITE */
 #include <fcntl.h>
 #include <inttypes.h>
 #include <pthread.h>
@@ -26,6 +27,9 @@
  * run and the last batch's tail is short, large enough to fill the device (measured on cfg2: 65536
  * beats 131072 by 10-20 %, 262144 loses 30 %) */
 #define DEFAULT_BATCH_READS 65536u
+
+#define PREALLOC_AHEAD (48ull << 20) /* prealloc_main: bytes of output pages kept allocated ahead of the text */
+#define PREALLOC_STEP (4ull << 20)
 
 /* ---- blocking FIFO of pointers ---------------------------------------------------------------- */
 typedef struct {
@@ -246,6 +250,10 @@ typedef struct {
   int out_populate;         /* madvise(MADV_POPULATE_WRITE) before the copy (FEM_SAM_POPULATE=0 turns it off) */
   int out_mmap;             /* tmpfs: chunks are copied into a shared mapping (pwrite holds the inode lock) */
   uint64_t out_alloc;       /* size the file has been extended to (writer thread only) */
+  /* page-cache pages of the output allocated ahead of the copies (prealloc_main) */
+  int prealloc, prealloc_stop;
+  uint64_t prealloc_goal;   /* guarded by mu: allocate up to this file offset */
+  pthread_cond_t prealloc_cv;
   int writes_outstanding;   /* guarded by mu; writer waits for 0 before the file is closed */
   pthread_cond_t writes_done;
   fifo q_free, q_parsed, q_work, q_write;
@@ -318,6 +326,15 @@ static void *reader_main(void *arg) {
  * range i+1 starts, the ranges together are the sequential parse of the file.  Anything else
  * (multi-line records, FASTA, CRLF, junk) aborts the run, which map_file repeats with the
  * sequential kseq-compatible reader. */
+/* byte where range i starts.  The first four ranges are 1/8, 1/8, 1/4 and 1/2 of the others: the readers
+ * start together, so the first SAM text is on its way to the file after an eighth of a batch's parse and
+ * device time instead of a whole one (the run is bound by the copies into the page cache, which can
+ * only start then) */
+static uint64_t par_range_start(const run_state *r, uint64_t i) {
+  static const uint64_t eighths[4] = {0, 1, 2, 4};
+  return i < 4 ? r->chunk_bytes * eighths[i] / 8 : (i - 3) * r->chunk_bytes;
+}
+
 static int64_t par_sync(run_state *r, uint64_t a, unsigned char *win, size_t win_cap) {
   if (a == 0) return 0;
   if (a >= r->file_size) return (int64_t)r->file_size;
@@ -347,8 +364,8 @@ static void *par_reader_main(void *arg) {
     pthread_mutex_unlock(&r->mu);
     if (i == UINT64_MAX) { fifo_push(&r->q_free, b); break; }
     const double t0 = femhost_now();
-    const int64_t lo = par_sync(r, i * r->chunk_bytes, win, win_cap);
-    const int64_t hi = i + 1 == r->n_chunks ? (int64_t)r->file_size : par_sync(r, (i + 1) * r->chunk_bytes, win, win_cap);
+    const int64_t lo = par_sync(r, par_range_start(r, i), win, win_cap);
+    const int64_t hi = i + 1 == r->n_chunks ? (int64_t)r->file_size : par_sync(r, par_range_start(r, i + 1), win, win_cap);
     int rc = lo < 0 || hi < lo ? 1 : 0;
     if (!rc) {
       const size_t n = (size_t)(hi - lo);
@@ -620,6 +637,12 @@ static void *writer_main(void *arg) {
       ++n_writes;
     }
     b->map_base = NULL;
+    if (n_writes && r->prealloc) {
+      pthread_mutex_lock(&r->mu);
+      if (r->out_off + PREALLOC_AHEAD > r->prealloc_goal) r->prealloc_goal = r->out_off + PREALLOC_AHEAD;
+      pthread_cond_signal(&r->prealloc_cv);
+      pthread_mutex_unlock(&r->mu);
+    }
     if (n_writes && r->out_mmap) { /* extend the file in big steps and map this batch's span of it */
       const uint64_t hi = r->out_off;
       uint64_t first = hi;
@@ -665,8 +688,35 @@ static void *writer_main(void *arg) {
   pthread_mutex_lock(&r->mu);
   while (r->writes_outstanding) pthread_cond_wait(&r->writes_done, &r->mu);
   pthread_mutex_unlock(&r->mu);
-  if (r->out_alloc && ftruncate(r->out_fd, (off_t)r->out_off) != 0) run_fail(r, "truncating the SAM file to its size failed");
-  r->tm.write = busy;
+  r->tm.write = busy; /* map_file_run cuts the file to its size once the allocator has stopped */
+  return NULL;
+}
+
+/* Allocates the output's page-cache pages ahead of the copies.  On tmpfs a first write to a page costs a
+ * page allocation under locks shared by every thread that writes the file (measured: 8-9 GB/s from six
+ * or sixteen copying threads alike); fallocate allocates them from one thread at 15 GB/s without
+ * zeroing, and copies into allocated pages scale with the threads (14 GB/s from six).  The pages past
+ * the end of the text go away with the final ftruncate. */
+static void *prealloc_main(void *arg) {
+  run_state *r = (run_state *)arg;
+  uint64_t done = 0;
+  pthread_mutex_lock(&r->mu);
+  for (;;) {
+    while (!r->prealloc_stop && r->prealloc_goal <= done) pthread_cond_wait(&r->prealloc_cv, &r->mu);
+    if (r->prealloc_stop) break;
+    const uint64_t goal = r->prealloc_goal;
+    pthread_mutex_unlock(&r->mu);
+    while (done < goal) {
+      if (fallocate(r->out_fd, FALLOC_FL_KEEP_SIZE, (off_t)done, (off_t)PREALLOC_STEP) != 0) { done = UINT64_MAX; break; } /* no room or not supported: page faults do it */
+      done += PREALLOC_STEP;
+      pthread_mutex_lock(&r->mu);
+      const int stop = r->prealloc_stop;
+      pthread_mutex_unlock(&r->mu);
+      if (stop) break;
+    }
+    pthread_mutex_lock(&r->mu);
+  }
+  pthread_mutex_unlock(&r->mu);
   return NULL;
 }
 
@@ -687,6 +737,7 @@ static int parallel_readable(const char *path, uint64_t *size) {
 /* threads that copy finished text into the output file: the page cache's per-file locks stop scaling
  * beyond about six (measured on tmpfs: 7.5 GB/s from six threads, the same from sixteen at three times the CPU time) */
 #define MAX_COPIERS 6
+static int max_copiers(void) { const char *e = getenv("FEM_SAM_COPIERS"); const int n = e ? atoi(e) : MAX_COPIERS; return n < 1 ? 1 : n > 64 ? 64 : n; }
 
 static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
                         int parallel, femgpu_stats *stats, femhost_map_timing *timing, int *restart) {
@@ -705,7 +756,8 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     const uint64_t per_batch = opt->batch_reads ? opt->batch_reads : DEFAULT_BATCH_READS;
     r.chunk_bytes = per_batch * 224; /* about per_batch reads of 100 bp; only the batch granularity depends on it */
     if (r.chunk_bytes < 4096) r.chunk_bytes = 4096;
-    r.n_chunks = (r.file_size + r.chunk_bytes - 1) / r.chunk_bytes;
+    r.n_chunks = 0;
+    while (par_range_start(&r, r.n_chunks) < r.file_size) ++r.n_chunks;
     r.readers_left = N_PAR_READERS;
   } else {
     r.rd = femhost_reader_open(reads_path);
@@ -734,7 +786,7 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   r.t_start = t_start;
   r.trace = getenv("FEM_TRACE") && atoi(getenv("FEM_TRACE")) != 0;
   const int n_gpu_threads = 2 * m->n_gpus, n_format = opt->n_threads, n_readers = parallel ? N_PAR_READERS : 1;
-  const int n_copiers = opt->n_threads < MAX_COPIERS ? opt->n_threads : MAX_COPIERS, n_workers = n_format + n_copiers;
+  const int n_copiers = opt->n_threads < max_copiers() ? opt->n_threads : max_copiers(), n_workers = n_format + n_copiers;
   r.n_batches = (size_t)(2 * n_gpu_threads + 6 + (parallel ? N_PAR_READERS : 0));
   if (m->n_pool != r.n_batches) {
     pool_free(m);
@@ -769,6 +821,25 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     if (parallel) pthread_create(&th_reader[i], NULL, par_reader_main, &pa[i]);
     else pthread_create(&th_reader[i], NULL, reader_main, &r);
   }
+  pthread_t th_prealloc;
+  pthread_cond_init(&r.prealloc_cv, NULL);
+  r.prealloc = r.out_mmap && !(getenv("FEM_SAM_PREALLOC") && atoi(getenv("FEM_SAM_PREALLOC")) == 0);
+  if (r.prealloc) {
+    struct statfs fs; /* only with room to spare: the pages ahead of the text are real memory until the end */
+    if (fstatfs(r.out_fd, &fs) != 0 || (uint64_t)fs.f_bavail * (uint64_t)fs.f_bsize < (1ull << 30)) r.prealloc = 0;
+  }
+  if (r.prealloc) {
+    /* a file of four-line FASTQ maps to about its own size of SAM text when most reads map once: those
+     * pages are allocated while the first batches are still being parsed and mapped, before the copies
+     * compete for the same locks; beyond that the allocator keeps PREALLOC_AHEAD in front of the text */
+    const char *pe = getenv("FEM_SAM_PREALLOC_PERCENT");
+    const uint64_t guess = parallel ? r.file_size / 100 * (uint64_t)(pe ? atoi(pe) : 110) : 0;
+    r.prealloc_goal = r.out_off + (guess > PREALLOC_AHEAD ? guess : PREALLOC_AHEAD);
+    struct statfs fs;
+    if (fstatfs(r.out_fd, &fs) == 0 && r.prealloc_goal > (uint64_t)fs.f_bavail * (uint64_t)fs.f_bsize / 4)
+      r.prealloc_goal = r.out_off + PREALLOC_AHEAD;
+    pthread_create(&th_prealloc, NULL, prealloc_main, &r);
+  }
   pthread_create(&th_writer, NULL, writer_main, &r);
   for (int i = 0; i < n_gpu_threads; ++i) {
     ga[i].r = &r; ga[i].gpu = i / 2; ga[i].slot = i % 2; ga[i].busy = 0;
@@ -785,6 +856,15 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   fifo_close(&r.q_work);
   fifo_close(&r.q_write);
   for (int i = 0; i < n_workers; ++i) { pthread_join(th_worker[i], NULL); r.tm.format += wa[i].busy; r.tm.write += wa[i].busy_write; }
+  if (r.prealloc) {
+    pthread_mutex_lock(&r.mu);
+    r.prealloc_stop = 1;
+    pthread_cond_signal(&r.prealloc_cv);
+    pthread_mutex_unlock(&r.mu);
+    pthread_join(th_prealloc, NULL);
+  }
+  pthread_cond_destroy(&r.prealloc_cv);
+  if ((r.out_alloc || r.prealloc) && ftruncate(r.out_fd, (off_t)r.out_off) != 0) run_fail(&r, "truncating the SAM file to its size failed");
   if (r.out_fd >= 0 && close(r.out_fd) != 0) run_fail(&r, "closing the SAM file failed");
   pthread_cond_destroy(&r.writes_done);
   r.tm.wall = femhost_now() - t_start;
