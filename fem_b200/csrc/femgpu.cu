@@ -23,6 +23,7 @@
 #include "k_index.cuh"
 #include "k_peak.cuh"
 #include "k_seed.cuh"
+#include "k_seed_multi.cuh"
 #include "k_trace.cuh"
 #include "k_sam.cuh"
 #include "k_verify.cuh"
@@ -178,7 +179,7 @@ struct femgpu_ctx {
   uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
-  int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan (tests force both)
+  int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan, 3 several read-strands per warp (tests force each)
   Slot slot[2];
   int last_slot = 0;
 };
@@ -254,7 +255,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
   else if (k == "device_traceback") c->device_traceback = value != 0;
-  else if (k == "seed_dp_mode" && value >= 0 && value <= 2) c->seed_dp_mode = (int)value;
+  else if (k == "seed_dp_mode" && value >= 0 && value <= 3) c->seed_dp_mode = (int)value;
   else return set_error(FEMGPU_EINVAL, "unknown option or bad value: %s=%lld", key, (long long)value);
   return 0;
 }

@@ -4,6 +4,8 @@ struct Plan { // derived from params + the batch
   int k, step, e, a, Q, s;
   int l_max, n_words_max, ns_max, w_max, lane_dp;
   size_t seed_smem;   // bytes per block of k_seed
+  int seed_R;         // > 0: k_seed_multi with this many read-strands per warp
+  uint32_t seed_words_per_rs;
   size_t cand_smem;   // bytes per block of k_cand
   uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
   size_t hash_smem;
@@ -38,6 +40,15 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   // one lane per group pays Q*W serial steps, the warp scan pays step*Q*ceil(W/32) rounds of ~7x the cost
   pl->lane_dp = c->seed_dp_mode == 1 ? 1 : c->seed_dp_mode == 2 ? 0 : pl->w_max <= 8 * pl->step;
   pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4; // 4 warps
+  // several read-strands per warp where the lane form leaves most lanes idle (k_seed_multi.cuh)
+  pl->seed_R = 0;
+  if ((c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
+    pl->seed_words_per_rs = seed_multi_words_per_rs(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step);
+    int R = 32 / pl->step;
+    while (R > 1 && 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH) > 56 * 1024) --R;
+    const size_t bytes = 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH);
+    if (bytes <= c->smem_optin) { pl->seed_R = R; pl->seed_smem = bytes; }
+  }
   pl->cand_smem = (size_t)4 * (c->sort_capacity + c->acc_capacity) * 8;
   // hash path: room for 4x the expected location-list total of a group on a uniform index
   uint32_t T = c->hash_slots;
@@ -167,8 +178,21 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.seed_freq = s.seed_freq.as<uint32_t>();
   sa.seed_start = s.seed_start.as<uint32_t>();
   sa.total_before = &dc->total_before;
-  if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
-  k_seed<<<(unsigned)((n_rs + 3) / 4), 128, pl.seed_smem, s.stream>>>(sa);
+  if (pl.seed_R > 0) {
+    SeedMultiArgs sm;
+    sm.a = sa;
+    sm.R = pl.seed_R;
+    sm.words_per_rs = pl.seed_words_per_rs;
+    sm.inv_step = (uint32_t)(0x100000000ull / (uint64_t)pl.step) + 1u;
+    sm.inv_Q = (uint32_t)(0x100000000ull / (uint64_t)pl.Q) + 1u;
+    sm.inv_stepQ = (uint32_t)(0x100000000ull / (uint64_t)(pl.step * pl.Q)) + 1u;
+    if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
+    const uint64_t per_block = 4ull * (uint64_t)pl.seed_R;
+    k_seed_multi<<<(unsigned)((n_rs + per_block - 1) / per_block), 128, pl.seed_smem, s.stream>>>(sm);
+  } else {
+    if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
+    k_seed<<<(unsigned)((n_rs + 3) / 4), 128, pl.seed_smem, s.stream>>>(sa);
+  }
   ++s.n_launches;
   CU(cudaGetLastError());
   cudaEventRecord(s.ev[1], s.stream);

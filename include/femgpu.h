@@ -139,7 +139,7 @@ void *femgpu_alloc_pinned(size_t bytes);
 void femgpu_free_pinned(void *p);
 
 /* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
- * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan),
+ * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan, 3 lane per group with several read-strands per warp),
  * "cand_mode" (0 automatic: near-pair path when a >= 1, hash path when a = 0; 1 sort path only;
  * 2 hash path first; 3 near-pair path first; 4 all-groups-at-once path first, the automatic
  * choice on sparse indexes), "hash_slots", "pair_bits", "pair_values" (0 automatic), "pair_layout" (32: the near-pair path reads a

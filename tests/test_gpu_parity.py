@@ -277,9 +277,9 @@ def test_double_buffered_submit_matches_sync(setup):
     assert tuple(a + b for a, b in zip(st0, st1)) == st_all
 
 
-@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("mode", [1, 2, 3])
 def test_seed_selection_forms_agree(setup, mode):
-    """k_seed's two DP forms (one lane per group / warp scan) must select the same seeds."""
+    """k_seed's DP forms (one lane per group / warp scan / several read-strands per warp) must select the same seeds."""
     seqs = [r[1] for r in setup.reads[:400]]
     setup.mapper.set_option("seed_dp_mode", mode)
     try:
