@@ -91,6 +91,7 @@ EXPORTS = {
     "femgpu_submit_batch": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Params), C.POINTER(Batch)]),
     "femgpu_wait_batch": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Result)]),
     "femgpu_set_reference_names": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_char_p)]),
+    "femgpu_clone_resident": (C.c_int, [C.c_void_p, C.c_void_p]),
     "femgpu_set_sam_inputs": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(SamInputs)]),
     "femgpu_candidates_batch": (C.c_int, [C.c_void_p, C.POINTER(Params), C.POINTER(Batch), C.POINTER(Candidates)]),
     "femgpu_sort_mappings": (None, [C.c_void_p, C.c_size_t]),
@@ -224,6 +225,10 @@ class Mapper:
         _check(self.lib.femgpu_upload_reference(self.h, n, seqs, lens))
         names = (C.c_char_p * n)(*[r[0] if isinstance(r[0], bytes) else str(r[0]).encode() for r in records])
         _check(self.lib.femgpu_set_reference_names(self.h, n, names))
+
+    def clone_resident_from(self, other):
+        """index + reference + record names device to device from another Mapper (src/FEM_map.c:136-143 once per node)"""
+        _check(self.lib.femgpu_clone_resident(self.h, other.h))
 
     # -- hot path -----------------------------------------------------------------------------
     @staticmethod

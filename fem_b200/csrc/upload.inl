@@ -158,3 +158,49 @@ extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char
   c->ref_canonical = (any_n & 2) == 0;
   return derive_occ32(c);
 }
+
+// The resident index, reference and record names of `src` copied device to device (NVLink peer copies
+// where the devices are peers, through the host otherwise): one read of the index file and one packing
+// of the reference serve every GPU of the node.  Stands in for the per-process load_index +
+// load_all_sequences of src/FEM_map.c:136-143 on the second and later devices.
+extern "C" int femgpu_clone_resident(femgpu_ctx *dst, const femgpu_ctx *src) {
+  if (!dst || !src || dst == src) return set_error(FEMGPU_EINVAL, "clone: bad contexts");
+  if (!src->lut.p || !src->n_rec) return set_error(FEMGPU_ESTATE, "clone: the source holds no index or no reference");
+  CU(cudaSetDevice(dst->device));
+  if (dst->device != src->device) {
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, dst->device, src->device) == cudaSuccess && can) {
+      const cudaError_t e = cudaDeviceEnablePeerAccess(src->device, 0);
+      if (e != cudaSuccess) cudaGetLastError(); // already enabled, or not possible: cudaMemcpyPeer stages through the host
+    }
+  }
+  cudaStream_t st = dst->slot[0].stream;
+  const uint64_t k_lut = (((uint64_t)1 << (2 * src->idx_k)) + 1) * sizeof(uint32_t);
+  const uint64_t n_w2 = (uint64_t)((src->ref_total + 31) / 32) * 2 + 4, n_wn = (uint64_t)((src->ref_total + 31) / 32) + 2;
+  struct { DBuf *d; const DBuf *s; uint64_t bytes; } parts[] = {
+      {&dst->lut, &src->lut, k_lut},
+      {&dst->occ, &src->occ, std::max<uint64_t>(src->n_occ, 1) * sizeof(uint64_t)},
+      {&dst->ref2, &src->ref2, n_w2 * 4},
+      {&dst->refn, &src->refn, n_wn * 4},
+      {&dst->rec_base, &src->rec_base, ((uint64_t)src->n_rec + 1) * 8},
+      {&dst->rec_len, &src->rec_len, (uint64_t)src->n_rec * 4},
+      {&dst->rnames, &src->rnames, src->have_rnames ? src->rnames.bytes : 0},
+      {&dst->rname_off, &src->rname_off, src->have_rnames ? ((uint64_t)src->n_rec + 1) * 4 : 0},
+  };
+  for (auto &pt : parts) {
+    if (!pt.bytes) continue;
+    if (pt.bytes > pt.s->bytes) return set_error(FEMGPU_ESTATE, "clone: source buffer smaller than its contents");
+    TRY(pt.d->reserve(pt.bytes + 64));
+    CU(cudaMemcpyPeerAsync(pt.d->p, dst->device, pt.s->p, src->device, pt.bytes, st));
+  }
+  CU(cudaStreamSynchronize(st));
+  dst->n_occ = src->n_occ;
+  dst->idx_k = src->idx_k;
+  dst->idx_step = src->idx_step;
+  dst->n_rec = src->n_rec;
+  dst->ref_total = src->ref_total;
+  dst->ref_has_n = src->ref_has_n;
+  dst->ref_canonical = src->ref_canonical;
+  dst->have_rnames = src->have_rnames;
+  return derive_occ32(dst);
+}

@@ -114,19 +114,25 @@ femhost_mapper *femhost_mapper_create(const char *ref_path, const char *index_pa
     lens[i] = femhost_record_length(&m->ref, i);
   }
   int rc = 0;
-  if (n_gpus > 1 && femhost_index_load(index_path, &idx)) rc = -1; /* one read of the file for all devices */
+  /* the file is read and the reference packed once, on the first device; the others receive copies
+   * device to device (FEM_CLONE_RESIDENT=0: every device loads for itself) */
+  const int clone = !(getenv("FEM_CLONE_RESIDENT") && atoi(getenv("FEM_CLONE_RESIDENT")) == 0);
+  if (n_gpus > 1 && !clone && femhost_index_load(index_path, &idx)) rc = -1;
   for (int g = 0; g < n_gpus && !rc; ++g) {
     m->ctx[g] = femgpu_create(gpu_ids ? gpu_ids[g] : g);
     if (!m->ctx[g]) { femhost_set_error(-2, "%s", femgpu_last_error()); rc = -2; break; }
     m->n_gpus = g + 1;
-    rc = n_gpus > 1 ? femgpu_upload_index(m->ctx[g], idx.k, idx.step, idx.lut, idx.lut_n, idx.occ, idx.n_occ)
-                    : femgpu_upload_index_file(m->ctx[g], index_path);
-    if (!rc) rc = femgpu_upload_reference(m->ctx[g], m->ref.n_records, seqs, lens);
-    if (!rc) { /* record names for the device's SAM text (k_sam) */
-      const char **rn = (const char **)malloc(m->ref.n_records * sizeof(char *));
-      for (uint32_t i = 0; i < m->ref.n_records; ++i) rn[i] = femhost_record_name(&m->ref, i);
-      rc = femgpu_set_reference_names(m->ctx[g], m->ref.n_records, rn);
-      free(rn);
+    if (g > 0 && clone) rc = femgpu_clone_resident(m->ctx[g], m->ctx[0]);
+    else {
+      rc = n_gpus > 1 && !clone ? femgpu_upload_index(m->ctx[g], idx.k, idx.step, idx.lut, idx.lut_n, idx.occ, idx.n_occ)
+                                : femgpu_upload_index_file(m->ctx[g], index_path);
+      if (!rc) rc = femgpu_upload_reference(m->ctx[g], m->ref.n_records, seqs, lens);
+      if (!rc) { /* record names for the device's SAM text (k_sam) */
+        const char **rn = (const char **)malloc(m->ref.n_records * sizeof(char *));
+        for (uint32_t i = 0; i < m->ref.n_records; ++i) rn[i] = femhost_record_name(&m->ref, i);
+        rc = femgpu_set_reference_names(m->ctx[g], m->ref.n_records, rn);
+        free(rn);
+      }
     }
     const char *tb = getenv("FEM_DEVICE_TRACEBACK"); /* "0": start/CIGAR of every mapping on the host */
     if (!rc && tb) rc = femgpu_set_option(m->ctx[g], "device_traceback", atoi(tb));

@@ -193,6 +193,10 @@ int femgpu_wait_batch(femgpu_ctx *ctx, int slot, femgpu_result *result);
  * femgpu_upload_reference (names as femhost_sam_header prints them); femgpu_set_sam_inputs applies to
  * the NEXT submit on that slot only. */
 int femgpu_set_reference_names(femgpu_ctx *ctx, uint32_t n_records, const char *const *names);
+/* Several GPUs in one process: the index, the packed reference and the record names resident in `src`
+ * copied device to device into `dst` (peer copies over NVLink where the devices are peers), instead of
+ * a second load_index / load_all_sequences (src/FEM_map.c:136-143, src/index.c:100-131) per device. */
+int femgpu_clone_resident(femgpu_ctx *dst, const femgpu_ctx *src);
 int femgpu_set_sam_inputs(femgpu_ctx *ctx, int slot, const femgpu_sam_inputs *inputs);
 
 /* Stage-level entry points (tests, profiling, and callers that keep their own verification).

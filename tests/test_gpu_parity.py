@@ -264,6 +264,29 @@ def test_device_sam_text_matches_oracle(setup, tmp_path):
     assert setup.mapper.last_sam is None
 
 
+def test_clone_resident_maps_the_same(setup):
+    """femgpu_clone_resident: a second context filled device to device (here on the same GPU; across GPUs in
+    tools/gpu_n2.sh) gives the same mappings and the same device SAM text as the one that was uploaded to."""
+    from fem_b200.api import Mapper
+    seqs = [r[1] for r in setup.reads[:300]]
+    names = [r[0].encode() for r in setup.reads[:300]]
+    quals = [r[2] for r in setup.reads[:300]]
+    f0, m0, st0 = setup.mapper.map_batch_sam(seqs, names, quals, setup.e, setup.a)
+    sam0 = setup.mapper.last_sam
+    other = Mapper(0)
+    try:
+        other.clone_resident_from(setup.mapper)
+        f1, m1, st1 = other.map_batch_sam(seqs, names, quals, setup.e, setup.a)
+        assert np.array_equal(f0, f1) and np.array_equal(m0, m1) and st0 == st1
+        assert sam0 is not None and other.last_sam is not None
+        assert np.array_equal(sam0[0], other.last_sam[0]) and sam0[2] == other.last_sam[2]
+        k, step, lut, occ = other.download_index()
+        k0, step0, lut0, occ0 = setup.mapper.download_index()
+        assert (k, step) == (k0, step0) and np.array_equal(lut, lut0) and np.array_equal(occ, occ0)
+    finally:
+        other.close()
+
+
 def test_double_buffered_submit_matches_sync(setup):
     seqs = [r[1] for r in setup.reads]
     half = len(seqs) // 2

@@ -15,5 +15,8 @@ fem_b200/bin/FEM index 12 4 $d/ref.fa $d/idx --gpu 2> /dev/null
 fem_b200/bin/FEM map -e 4 -t 8 --ref $d/ref.fa --index $d/idx --read1 $d/reads.fq -o $d/one.sam 2> $d/one.err; echo "single rc=$?"
 fem_b200/bin/FEM map -e 4 -t 8 --gpus $N --ref $d/ref.fa --index $d/idx --read1 $d/reads.fq -o $d/multi.sam 2> $d/multi.err; echo "--gpus $N rc=$?"
 timeout 600 $TR -m fem_b200.shard -e 4 -t 4 --ref $d/ref.fa --index $d/idx --read1 $d/reads.fq -o $d/shard.sam 2> $d/shard.err; echo "shard rc=$?"
+FEM_CLONE_RESIDENT=0 fem_b200/bin/FEM map -e 4 -t 8 --gpus $N --ref $d/ref.fa --index $d/idx --read1 $d/reads.fq -o $d/multi0.sam 2> $d/multi0.err; echo "--gpus $N, every device loads for itself rc=$?"
+cmp $d/one.sam $d/multi0.sam && echo "FEM map --gpus $N (no clone) == single"
+grep -i "resident\|load" $d/multi.err $d/multi0.err | head
 cmp $d/one.sam $d/multi.sam && echo "FEM map --gpus $N == single"; cmp $d/one.sam $d/shard.sam && echo "torchrun shard driver == single"
 grep "number of" $d/one.err | tr '\n' ';'; echo; grep "number of\|Time" $d/shard.err | tr '\n' ';'; echo
