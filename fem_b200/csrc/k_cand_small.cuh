@@ -116,7 +116,8 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
     return;
   }
   __syncwarp();
-  // ---- F5: one lane per group truncates the last seed's entries --------------------------------------
+  // ---- F5: the last seed of a group only contributes entries up to the largest entry of the others: one
+  //      lane per group finds that bound (kept in sv, free until the count), one lane per entry applies it
   for (uint32_t g = lane; g < step; g += 32) {
     uint64_t mv = 0;
     bool has = false;
@@ -125,9 +126,12 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
       if (m != FEM_SENTINEL && (!has || m > mv)) { mv = m; has = true; }
     }
     dead[g] = has ? 0 : 1;
-    const uint32_t lo = eo[g * Q + Q - 1], hi = eo[g * Q + Q];
-    for (uint32_t t = lo; t < hi; ++t)
-      if (!has || (vals[t] != FEM_SENTINEL && vals[t] > mv)) vals[t] = FEM_SENTINEL;
+    sv[g] = mv;
+  }
+  __syncwarp();
+  for (uint32_t t = lane; t < T; t += 32) {
+    const uint32_t g = eg[t];
+    if (t >= eo[g * Q + Q - 1] && (dead[g] || (vals[t] != FEM_SENTINEL && vals[t] > sv[g]))) vals[t] = FEM_SENTINEL;
   }
   __syncwarp();
   // ---- exact: one lane per entry ---------------------------------------------------------------------

@@ -137,8 +137,10 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
     aln_store(out, start, 1, cig, (uint32_t)o);
     return;
   }
-  // :303-338 the band again, 32-bit words, D0 and HP of every column kept
-  uint32_t D0s[LCAP], HPs[LCAP];
+  // :303-338 the band again, 32-bit words; the low 16 bits of D0 and HP of every column kept in one
+  // word (the band is 2e + 1 <= 15 bits wide; the walk below only looks at bit positions 0..15 and leaves
+  // anything else to the host): half the local-memory traffic of two 32-bit histories
+  uint32_t hist[LCAP];
   {
     uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0, VP = 0, VN = 0;
     uint64_t g = g0;
@@ -158,8 +160,7 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
       X = D0 >> 1;
       VN = X & HP;
       VP = HN | ~(X | HP);
-      D0s[i] = D0;
-      HPs[i] = HP;
+      hist[i] = (D0 & 0xFFFFu) | (HP << 16);
       p0 >>= 1; p1 >>= 1; p2 >>= 1; p3 >>= 1; p4 >>= 1;
     }
   }
@@ -178,8 +179,8 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   } while (0)
   while (tp >= 0 && (used != dist || tp == l - 1) && !fail) {
     const uint32_t sh = (uint32_t)bit & 31u; // the reference shifts by `bit`; out-of-range shifts are UB there
-    if (bit < 0 || bit > 31) { fail = true; break; }
-    const uint32_t d0 = (D0s[tp] >> sh) & 1u;
+    if (bit < 0 || bit > 15) { fail = true; break; }
+    const uint32_t h = hist[tp] >> sh, d0 = h & 1u;
     const bool same = rp >= 0 && ref_code_fetch<HAS_N>(A.ref, g0 + (uint64_t)rp) == text[tp];
     if (d0 && same) { // match
       --tp; --rp;
@@ -187,7 +188,7 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
     } else if (!d0) { // mismatch
       --tp; --rp; ++used;
       if (run == OP_S || run == OP_M) ++run_n; else CLOSE_RUN(OP_M);
-    } else if ((HPs[tp] >> sh) & 1u) { // insertion: a read base only
+    } else if ((h >> 16) & 1u) { // insertion: a read base only
       --tp; ++bit; ++used; ++start;
       if (run == OP_S || run == OP_I) ++run_n; else CLOSE_RUN(OP_I);
     } else { // deletion: a reference base only
