@@ -83,18 +83,30 @@ static int run_sam(femgpu_ctx *c, Slot &s) {
   a.host_flag = s.sam_host.as<uint8_t>();
   a.text_off = s.sam_off.as<uint64_t>();
   a.n_flagged = &dc->sam_flagged;
+  TRY(s.sam_big_list.reserve(n * 4ull + 16));
+  TRY(s.sam_big_ord.reserve(s.n_maps * 2ull + 16));
+  TRY(s.sam_big_rec_off.reserve(s.n_maps * 4ull + 16));
+  a.big_list = s.sam_big_list.as<uint32_t>();
+  a.n_big = &dc->sam_big;
+  a.big_ord = s.sam_big_ord.as<uint16_t>();
+  a.big_rec_off = s.sam_big_rec_off.as<uint32_t>();
+  const unsigned big_grid = (unsigned)c->sm_count * 2u;
+  const size_t big_smem = 4 * (size_t)SAM_BIG_MAX * 10;
   a.text = nullptr;
   const unsigned grid = (n + 127) / 128;
   k_sam_len<<<grid, 128, 0, s.stream>>>(a);
+  CU(cudaFuncSetAttribute(k_sam_big_len, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)big_smem));
+  k_sam_big_len<<<big_grid, 128, big_smem, s.stream>>>(a); // reads k_sam_len listed (65..SAM_BIG_MAX mappings); idles without any
   k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>());
   k_scan_blocks<<<1, 32, 0, s.stream>>>(s.sam_blocks.as<uint64_t>(), n_blocks, (uint64_t *)&dc->sam_total);
   k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, s.stream>>>(s.sam_bytes.as<uint32_t>(), n, s.sam_blocks.as<uint64_t>(),
                                                      s.sam_off.as<uint64_t>(), (uint64_t *)&dc->sam_total);
-  s.n_launches += 4;
+  s.n_launches += 5;
   CU(cudaGetLastError());
   Counters hc;
   TRY(read_counters(s, &hc));
   s.sam_total = hc.sam_total;
+  const uint64_t n_big = hc.sam_big;
   s.sam_flagged = hc.sam_flagged;
   if (s.sam_total) {
     TRY(s.sam_text.reserve(s.sam_total + 16));
@@ -106,6 +118,10 @@ static int run_sam(femgpu_ctx *c, Slot &s) {
     CU(cudaFuncSetAttribute(k_sam_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * SAM_IMAGE_MAX)));
     k_sam_write<<<grid, 128, 4 * image, s.stream>>>(a, (uint32_t)image);
     ++s.n_launches;
+    if (n_big) {
+      k_sam_big_write<<<big_grid, 128, 0, s.stream>>>(a);
+      ++s.n_launches;
+    }
     CU(cudaGetLastError());
   }
   return 0;

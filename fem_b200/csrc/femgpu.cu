@@ -106,6 +106,7 @@ struct Counters {
   unsigned long long cols_executed;
   unsigned long long sam_total;
   unsigned long long sam_flagged; // reads k_sam left to the host
+  unsigned long long sam_big;     // reads with 65..SAM_BIG_MAX mappings (k_sam_big_*)
   uint32_t overflow_count;
   int error_flag;
 };
@@ -123,6 +124,7 @@ struct Slot {
   DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
   // SAM text on the device (k_sam): inputs of the batch, per-read sizes / offsets / flags, the text
   DBuf names, name_off, quals, has_qual, sam_bytes, sam_host, sam_off, sam_blocks, sam_text;
+  DBuf sam_big_list, sam_big_ord, sam_big_rec_off;
   HBuf h_sam_text, h_sam_off, h_sam_host;
   femgpu_sam_inputs sam_in{};
   bool sam_pending = false, sam_on = false;
@@ -224,7 +226,8 @@ static void slot_release(Slot &s) {
                &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
                &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
                &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first,
-               &s.names, &s.name_off, &s.quals, &s.has_qual, &s.sam_bytes, &s.sam_host, &s.sam_off, &s.sam_blocks, &s.sam_text};
+               &s.names, &s.name_off, &s.quals, &s.has_qual, &s.sam_bytes, &s.sam_host, &s.sam_off, &s.sam_blocks, &s.sam_text,
+               &s.sam_big_list, &s.sam_big_ord, &s.sam_big_rec_off};
   for (auto *b : d) b->release();
   HBuf *h[] = {&s.h_sam_text, &s.h_sam_off, &s.h_sam_host, &s.h_aln, &s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
   for (auto *b : h) b->release();

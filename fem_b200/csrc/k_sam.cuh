@@ -15,6 +15,7 @@
 #include "common.cuh"
 #include "k_trace.cuh"
 
+#define SAM_BIG_MAX 2048u    // most mappings of a read the device still formats (k_sam_big_*)
 #define SAM_IMAGE_MAX 24576u // most bytes of shared memory per warp in k_sam_write (four warps per block)
 
 struct SamArgs {
@@ -33,6 +34,11 @@ struct SamArgs {
   uint32_t *read_bytes;       // out (length pass): bytes of text of each read
   uint8_t *host_flag;         // out (length pass): 1 = left to the host
   unsigned long long *n_flagged; // out (length pass): how many
+  // reads with 65..SAM_BIG_MAX mappings: a warp per read (k_sam_big_len / k_sam_big_write)
+  uint32_t *big_list;         // read numbers, in no particular order
+  unsigned long long *n_big;
+  uint16_t *big_ord;          // per mapping slot: which of the read's mappings is printed r-th
+  uint32_t *big_rec_off;      // per mapping slot: offset of the r-th record within the read's text
   const uint64_t *text_off;   // in (text pass): exclusive scan of read_bytes
   char *text;                 // out (text pass)
 };
@@ -62,7 +68,60 @@ struct SamOut {
   }
 };
 
-// the records of read i (n >= 1 mappings, not left to the host); returns the bytes.  seq_at: MODE 2,
+// one record: mapping m of read i (bases at off, l long), primary (SEQ/QUAL present) or not
+template <int MODE>
+__device__ __forceinline__ void sam_emit_record(const SamArgs &A, SamOut<MODE> &o, uint32_t i, uint64_t m, bool primary,
+                                                const char *name, uint32_t name_l, uint64_t off, uint32_t l,
+                                                uint32_t *seq_at, bool *with_qual) {
+  const ulonglong2 rec = A.maps[m];
+  const uint32_t *al = A.aln + m * ALN_WORDS;
+  const uint32_t w0 = al[0];
+  const int start = (int)(int16_t)(uint16_t)w0;
+  const uint32_t n_cigar = (w0 >> 16) & 0xFFu, md_len = w0 >> 24;
+  const uint32_t dir = (uint32_t)(rec.y >> 32) & 0xFFu, dist = (uint32_t)(rec.y >> 40) & 0xFFu;
+  const uint32_t r = (uint32_t)(rec.x >> 32), pos = (uint32_t)start + (uint32_t)rec.x; // src/align.c:80
+  o.mem(name, name_l);
+  o.ch('\t');
+  o.num((dir ? 16u : 0u) | (primary ? 0u : 256u));
+  o.ch('\t');
+  o.mem(A.rnames + A.rname_off[r], A.rname_off[r + 1] - A.rname_off[r]);
+  o.ch('\t');
+  o.num(pos + 1u);
+  o.lit("\t255\t");
+  if (n_cigar == 0) o.ch('*');
+  for (uint32_t ci = 0; ci < n_cigar; ++ci) {
+    const uint32_t c = (al[1 + (ci >> 1)] >> (16 * (ci & 1))) & 0xFFFFu;
+    o.num(c >> 2);
+    o.ch("MID"[c & 3u]);
+  }
+  o.lit("\t*\t0\t0\t");
+  if (primary) { // the primary record carries SEQ/QUAL in the file's orientation (src/align.c:79,87)
+    const bool q = A.has_qual[i] && A.quals[off] != ' '; // htslib sam.c:3047 prints '*' otherwise
+    if (MODE == 2) {
+      *seq_at = o.n;
+      *with_qual = q;
+      o.n += l;
+      o.ch('\t');
+      if (q) o.n += l;
+      else o.ch('*');
+    } else {
+      o.mem(A.bases + off, l); // canonical reads only (others are left to the host): printed as they are
+      o.ch('\t');
+      if (q) o.mem(A.quals + off, l);
+      else o.ch('*');
+    }
+  } else {
+    o.lit("*\t*");
+  }
+  o.lit("\tNM:i:");
+  o.num(dist);
+  o.lit("\tMD:Z:");
+  if (MODE) for (uint32_t k = 0; k < md_len; ++k) o.p[o.n + k] = (char)((al[10 + (k >> 2)] >> (8 * (k & 3))) & 0xFFu);
+  o.n += md_len;
+  o.ch('\n');
+}
+
+// the records of read i (1 <= n <= 64 mappings, not left to the host); returns the bytes.  seq_at: MODE 2,
 // offset of SEQ within the text; with_qual: MODE 2, QUAL follows SEQ + tab (else '*' was written)
 template <int MODE>
 __device__ __forceinline__ uint32_t sam_emit_read(const SamArgs &A, uint32_t i, uint64_t m0, uint32_t n, char *p,
@@ -88,55 +147,7 @@ __device__ __forceinline__ uint32_t sam_emit_read(const SamArgs &A, uint32_t i, 
   SamOut<MODE> o;
   o.p = p;
   o.n = 0;
-  for (uint32_t mi = 0; mi < n; ++mi) {
-    const uint64_t m = m0 + ord[mi];
-    const ulonglong2 rec = A.maps[m];
-    const uint32_t *al = A.aln + m * ALN_WORDS;
-    const uint32_t w0 = al[0];
-    const int start = (int)(int16_t)(uint16_t)w0;
-    const uint32_t n_cigar = (w0 >> 16) & 0xFFu, md_len = w0 >> 24;
-    const uint32_t dir = (uint32_t)(rec.y >> 32) & 0xFFu, dist = (uint32_t)(rec.y >> 40) & 0xFFu;
-    const uint32_t r = (uint32_t)(rec.x >> 32), pos = (uint32_t)start + (uint32_t)rec.x; // src/align.c:80
-    o.mem(name, name_l);
-    o.ch('\t');
-    o.num((dir ? 16u : 0u) | (mi ? 256u : 0u));
-    o.ch('\t');
-    o.mem(A.rnames + A.rname_off[r], A.rname_off[r + 1] - A.rname_off[r]);
-    o.ch('\t');
-    o.num(pos + 1u);
-    o.lit("\t255\t");
-    if (n_cigar == 0) o.ch('*');
-    for (uint32_t ci = 0; ci < n_cigar; ++ci) {
-      const uint32_t c = (al[1 + (ci >> 1)] >> (16 * (ci & 1))) & 0xFFFFu;
-      o.num(c >> 2);
-      o.ch("MID"[c & 3u]);
-    }
-    o.lit("\t*\t0\t0\t");
-    if (mi == 0) { // the primary record carries SEQ/QUAL in the file's orientation (src/align.c:79,87)
-      const bool q = A.has_qual[i] && A.quals[off] != ' '; // htslib sam.c:3047 prints '*' otherwise
-      if (MODE == 2) {
-        *seq_at = o.n;
-        *with_qual = q;
-        o.n += l;
-        o.ch('\t');
-        if (q) o.n += l;
-        else o.ch('*');
-      } else {
-        o.mem(A.bases + off, l); // canonical reads only (others are left to the host): printed as they are
-        o.ch('\t');
-        if (q) o.mem(A.quals + off, l);
-        else o.ch('*');
-      }
-    } else {
-      o.lit("*\t*");
-    }
-    o.lit("\tNM:i:");
-    o.num(dist);
-    o.lit("\tMD:Z:");
-    if (MODE) for (uint32_t k = 0; k < md_len; ++k) o.p[o.n + k] = (char)((al[10 + (k >> 2)] >> (8 * (k & 3))) & 0xFFu);
-    o.n += md_len;
-    o.ch('\n');
-  }
+  for (uint32_t mi = 0; mi < n; ++mi) sam_emit_record<MODE>(A, o, i, m0 + ord[mi], mi == 0, name, name_l, off, l, seq_at, with_qual);
   return o.n;
 }
 
@@ -149,6 +160,11 @@ __global__ void __launch_bounds__(128) k_sam_len(SamArgs A) {
   A.read_bytes[i] = 0;
   A.host_flag[i] = 0;
   if (n == 0) return;
+  if (n > 64 && n <= SAM_BIG_MAX) { // a warp sorts and measures this one
+    A.host_flag[i] = 2;
+    A.big_list[atomicAdd(A.n_big, 1ull)] = i;
+    return;
+  }
   bool host = n > 64;
   for (uint32_t j = 0; j < n && !host; ++j) {
     const uint32_t w0 = A.aln[(m0 + j) * ALN_WORDS];
@@ -194,7 +210,10 @@ __global__ void __launch_bounds__(128) k_sam_write(SamArgs A, uint32_t image) {
   }
   const uint32_t skew = (uint32_t)(t0 & 15u);
   const uint64_t total = (t1 - t0) + skew;
-  if (total > image) {
+  // a read of k_sam_big_write inside the span: its bytes are not in the image, so no image for this warp
+  const bool big_here = __any_sync(0xffffffffu, live && n > 64);
+  if (n > 64) n = 0;
+  if (total > image || big_here) {
     if (n) sam_emit_read<1>(A, i, m0, n, A.text + A.text_off[i], nullptr, nullptr);
     return;
   }
@@ -226,5 +245,113 @@ __global__ void __launch_bounds__(128) k_sam_write(SamArgs A, uint32_t image) {
     if (c >= skew && c + 16u <= tot) *reinterpret_cast<uint4 *>(dst + c) = *reinterpret_cast<const uint4 *>(img + c);
     else
       for (uint32_t k = max(c, skew); k < min(c + 16u, tot); ++k) dst[k] = img[k];
+  }
+}
+
+// ---- reads with 65..SAM_BIG_MAX mappings ---------------------------------------------------------------
+// klib's radix sort is not stable beyond 64 records (src/ksort.h:113-151), but with pairwise different
+// keys every sort gives the same order: a warp sorts (key, index) by a bitonic network in shared memory,
+// hands reads with two equal keys (or an alignment left to the host) to the host, and otherwise measures
+// the records in their order.  One lane per record then writes it (k_sam_big_write).
+__global__ void __launch_bounds__(128) k_sam_big_len(SamArgs A) {
+  extern __shared__ __align__(16) unsigned char sam_big_smem[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, warps = gridDim.x * (blockDim.x >> 5);
+  uint64_t *key = reinterpret_cast<uint64_t *>(sam_big_smem) + (size_t)warp * SAM_BIG_MAX;
+  uint16_t *idx = reinterpret_cast<uint16_t *>(sam_big_smem + (size_t)(blockDim.x >> 5) * SAM_BIG_MAX * 8) + (size_t)warp * SAM_BIG_MAX;
+  const uint64_t n_big = *A.n_big;
+  for (uint64_t b = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp; b < n_big; b += warps) {
+    const uint32_t i = A.big_list[b];
+    const uint64_t m0 = A.rs_map_first[2ull * i];
+    const uint32_t n = (uint32_t)(A.rs_map_first[2ull * i + 2] - m0);
+    uint32_t P = 128;
+    while (P < n) P <<= 1;
+    bool host = false;
+    for (uint32_t j = lane; j < P; j += 32) {
+      uint64_t kj = ~0ull;
+      if (j < n) {
+        kj = sam_key(A.maps[m0 + j]);
+        const uint32_t w0 = A.aln[(m0 + j) * ALN_WORDS];
+        host |= ((w0 >> 16) & 0xFFu) == ALN_HOST || (w0 >> 24) == ALN_HOST;
+      }
+      key[j] = kj;
+      idx[j] = (uint16_t)j;
+    }
+    host = __any_sync(0xffffffffu, host);
+    __syncwarp();
+    if (!host) {
+      for (uint32_t k = 2; k <= P; k <<= 1)
+        for (uint32_t d = k >> 1; d > 0; d >>= 1) {
+          for (uint32_t t = lane; t < (P >> 1); t += 32) {
+            const uint32_t lo = ((t & ~(d - 1)) << 1) | (t & (d - 1)), hi = lo | d; // the pair t of this stage
+            const bool up = (lo & k) == 0;
+            const uint64_t a = key[lo], c = key[hi];
+            if ((a > c) == up) {
+              key[lo] = c; key[hi] = a;
+              const uint16_t x = idx[lo]; idx[lo] = idx[hi]; idx[hi] = x;
+            }
+          }
+          __syncwarp();
+        }
+      for (uint32_t j = lane; j + 1 < n; j += 32) host |= key[j] == key[j + 1];
+      host = __any_sync(0xffffffffu, host);
+    }
+    if (host) {
+      if (lane == 0) { A.host_flag[i] = 1; A.read_bytes[i] = 0; atomicAdd(A.n_flagged, 1ull); }
+      __syncwarp();
+      continue;
+    }
+    const uint64_t off = A.read_off[i];
+    const uint32_t l = (uint32_t)(A.read_off[i + 1] - off);
+    const char *name = A.names + A.name_off[i];
+    uint32_t name_l = 0;
+    while (name[name_l]) ++name_l;
+    uint32_t running = 0;
+    for (uint32_t r0 = 0; r0 < n; r0 += 32) {
+      const uint32_t r = r0 + lane;
+      uint32_t len = 0;
+      if (r < n) {
+        SamOut<0> o;
+        o.p = nullptr;
+        o.n = 0;
+        sam_emit_record<0>(A, o, i, m0 + idx[r], r == 0, name, name_l, off, l, nullptr, nullptr);
+        len = o.n;
+      }
+      uint32_t incl = len;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o2 = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((int)lane >= d) incl += o2;
+      }
+      if (r < n) {
+        A.big_ord[m0 + r] = idx[r];
+        A.big_rec_off[m0 + r] = running + incl - len;
+      }
+      running += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) { A.read_bytes[i] = running; A.host_flag[i] = 0; }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(128) k_sam_big_write(SamArgs A) {
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, warps = gridDim.x * (blockDim.x >> 5);
+  const uint64_t n_big = *A.n_big;
+  for (uint64_t b = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp; b < n_big; b += warps) {
+    const uint32_t i = A.big_list[b];
+    if (A.host_flag[i]) continue;
+    const uint64_t m0 = A.rs_map_first[2ull * i];
+    const uint32_t n = (uint32_t)(A.rs_map_first[2ull * i + 2] - m0);
+    const uint64_t off = A.read_off[i];
+    const uint32_t l = (uint32_t)(A.read_off[i + 1] - off);
+    const char *name = A.names + A.name_off[i];
+    uint32_t name_l = 0;
+    while (name[name_l]) ++name_l;
+    char *text = A.text + A.text_off[i];
+    for (uint32_t r = lane; r < n; r += 32) {
+      SamOut<1> o;
+      o.p = text + A.big_rec_off[m0 + r];
+      o.n = 0;
+      sam_emit_record<1>(A, o, i, m0 + A.big_ord[m0 + r], r == 0, name, name_l, off, l, nullptr, nullptr);
+    }
   }
 }

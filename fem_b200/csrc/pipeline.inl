@@ -42,7 +42,10 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4; // 4 warps
   // several read-strands per warp where the lane form leaves most lanes idle (k_seed_multi.cuh)
   pl->seed_R = 0;
-  if ((c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
+  // (automatic choice: only while the lookup table is small enough to stay in L2 -- k <= 12, 67 MB; with
+  //  k = 14 its gathers go to HBM and the one-read-strand form's larger number of warps in flight wins:
+  //  cfg5 10 ms against 22 ms)
+  if (((c->seed_dp_mode == 0 && pl->k <= 12) || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
     pl->seed_words_per_rs = seed_multi_words_per_rs(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step);
     int R = 32 / pl->step;
     while (R > 1 && 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH) > 56 * 1024) --R;

@@ -242,10 +242,12 @@ def test_device_sam_text_matches_oracle(setup, tmp_path):
     assert setup.mapper.last_sam is not None
     off, host, text = setup.mapper.last_sam
     assert len(text) == int(off[-1])
-    n_dev = n_host = 0
+    n_dev = n_host = n_big = n_big_dev = 0
     for i, name in enumerate(names):
         got = text[int(off[i]):int(off[i + 1])]
         n = int(first[i + 1] - first[i])
+        n_big += n > 64
+        n_big_dev += n > 64 and not host[i]
         if host[i]:
             assert got == b"" and (n > 64 or not set(seqs[i]) <= set(b"ACGTN") or setup.tag == "withN"), "read %d" % i
             n_host += 1
@@ -259,6 +261,9 @@ def test_device_sam_text_matches_oracle(setup, tmp_path):
         assert got == exp, "read %d: %r != %r" % (i, got[:300], exp[:300])
         n_dev += n > 0
     assert n_dev > 0 and n_dev >= n_host or setup.tag.startswith("rep")
+    # reads with 65..2048 mappings go through k_sam_big_* unless two of their records share a sort key
+    assert n_big == 0 or n_big_dev > 0, (n_big, n_big_dev)
+    print("%s: %d reads formatted on the device (%d of %d with more than 64 records), %d on the host" % (setup.tag, n_dev, n_big_dev, n_big, n_host))
     # the inputs apply to one submit only
     setup.mapper.map_batch(seqs[:20], setup.e, setup.a)
     assert setup.mapper.last_sam is None
