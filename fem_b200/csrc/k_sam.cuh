@@ -333,8 +333,14 @@ __global__ void __launch_bounds__(128) k_sam_big_len(SamArgs A) {
   }
 }
 
+#define SAM_BIG_IMAGE 8192u // bytes of shared memory per warp in k_sam_big_write
+
+// 32 consecutive records of a read own one contiguous span of its text: built in a shared-memory image
+// by one lane per record, written out as 16-byte stores (as in k_sam_write); longer spans byte-wise.
 __global__ void __launch_bounds__(128) k_sam_big_write(SamArgs A) {
+  __shared__ __align__(16) char sam_big_img[4 * SAM_BIG_IMAGE];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, warps = gridDim.x * (blockDim.x >> 5);
+  char *img = sam_big_img + (size_t)warp * SAM_BIG_IMAGE;
   const uint64_t n_big = *A.n_big;
   for (uint64_t b = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp; b < n_big; b += warps) {
     const uint32_t i = A.big_list[b];
@@ -346,12 +352,32 @@ __global__ void __launch_bounds__(128) k_sam_big_write(SamArgs A) {
     const char *name = A.names + A.name_off[i];
     uint32_t name_l = 0;
     while (name[name_l]) ++name_l;
-    char *text = A.text + A.text_off[i];
-    for (uint32_t r = lane; r < n; r += 32) {
-      SamOut<1> o;
-      o.p = text + A.big_rec_off[m0 + r];
-      o.n = 0;
-      sam_emit_record<1>(A, o, i, m0 + A.big_ord[m0 + r], r == 0, name, name_l, off, l, nullptr, nullptr);
+    const uint64_t t_read = A.text_off[i];
+    const uint32_t read_len = (uint32_t)(A.text_off[i + 1] - t_read);
+    for (uint32_t r0 = 0; r0 < n; r0 += 32) {
+      const uint32_t r = r0 + lane;
+      const uint32_t mine = r < n ? A.big_rec_off[m0 + r] : 0u;
+      const uint32_t s0 = __shfl_sync(0xffffffffu, mine, 0);
+      const uint32_t s1 = r0 + 32 < n ? A.big_rec_off[m0 + r0 + 32] : read_len;
+      const uint64_t t0 = t_read + s0;
+      const uint32_t skew = (uint32_t)(t0 & 15u), tot = (s1 - s0) + skew;
+      const bool staged = tot <= SAM_BIG_IMAGE;
+      if (r < n) {
+        SamOut<1> o;
+        o.p = staged ? img + skew + (mine - s0) : A.text + t_read + mine;
+        o.n = 0;
+        sam_emit_record<1>(A, o, i, m0 + A.big_ord[m0 + r], r == 0, name, name_l, off, l, nullptr, nullptr);
+      }
+      __syncwarp();
+      if (staged) {
+        char *dst = A.text + (t0 - skew);
+        for (uint32_t c = lane * 16u; c < tot; c += 512u) {
+          if (c >= skew && c + 16u <= tot) *reinterpret_cast<uint4 *>(dst + c) = *reinterpret_cast<const uint4 *>(img + c);
+          else
+            for (uint32_t k = max(c, skew); k < min(c + 16u, tot); ++k) dst[k] = img[k];
+        }
+        __syncwarp();
+      }
     }
   }
 }
