@@ -113,8 +113,24 @@ class ClockSampler:
 
     def __init__(self, gpu_index):
         self.gpu, self.proc, self.lines = gpu_index, None, []
+        self.nvml, self.samples, self.halt = None, [], False
 
     def start(self):
+        # NVML polled every 2 ms from a thread: the timed region of the resident leg is tens of milliseconds,
+        # shorter than nvidia-smi's start-up; nvidia-smi -lms stays as the fall-back
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = int(vis.split(",")[self.gpu]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else self.gpu
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -124,11 +140,40 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        while not self.halt:
+            try:
+                sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                try:
+                    why = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    why = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                try:
+                    power = n.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:
+                    power = 0.0
+                self.samples.append((sm, why, power))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def _stop_nvml(self):
+        self.halt = True
+        self.t.join(timeout=2)
+        bits = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
+        sm = sorted(x[0] for x in self.samples)
+        reasons = sorted(k for k, b in bits.items() if any(x[1] & b for x in self.samples))
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(sm), "power_w_max": max((x[2] for x in self.samples), default=0.0), "source": "nvml, 2 ms period"}
+
     def _pump(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml:
+            return self._stop_nvml()
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
