@@ -418,6 +418,9 @@ def run_ours(args):
     roofline = {"kernel": names[top], "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                 "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": algo[names[top]],
                 "peak_source": peak_src, "share_of_step": per[top] / sum(per)}
+    if traffic:  # what the kernel really moves (random 8-byte gathers cost a 64-byte DRAM burst each), for the same time
+        roofline["traffic_gbs"] = traffic / (per[top] * 1e-3) / 1e9
+        roofline["traffic_frac_of_peak"] = roofline["traffic_gbs"] / hbm_peak
     giops = (C.c_double * 3)()
     _check(lib.femgpu_measure_int32_peak(ctx, C.byref(giops)))
     int_ops = 24.0 * cols + 12.0 * w["e"] * n_cand  # 24 integer ops per executed column
