@@ -161,3 +161,55 @@ def test_reader_paths_agree(big):
     with open(big["fq"], "rb") as f, gz.open(zipped, "wb", compresslevel=1) as g:
         g.write(f.read())
     assert run(zipped) == big["want"]
+
+
+def test_cli_ragged_low_complexity_and_empty_inputs(tmp_path):
+    """the whole engine on a file that mixes read lengths from 12 to 1024 bases, N-only reads, duplicates and
+    homopolymer / tandem-repeat reads with thousands of records (device SAM text, k_sam_big_*, host formatter
+    and global-scratch candidates in one run), then on a file with one read and on an empty file"""
+    import numpy as np
+    from fem_b200.host import FEM_BINARY
+    rng = np.random.default_rng(77)
+    records = synth.random_reference(123, [150_000, 80_000, 2_000], 0.15)
+    tail = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), 20_000))
+    records.append(("lowcomplexity", b"A" * 3000 + b"ACGT" * 900 + b"AC" * 1500 + tail))
+    low = records[3][1]
+    reads = synth.simulate_reads(11, records[:3], 1500, 100, 3, lengths=[12, 20, 35, 48, 64, 100, 101, 150, 251, 400, 1024])
+    reads += [("polyA", b"A" * 100, b"I" * 100), ("allN", b"N" * 80, b"#" * 80), ("acgt", b"ACGT" * 25, b"I" * 100)]
+    reads += [("t%d" % i, low[3000 + 4 * i:3100 + 4 * i], b"5" * 100) for i in range(60)]
+    reads += [("dup%d" % i, reads[7][1], reads[7][2]) for i in range(50)]
+    order = rng.permutation(len(reads))
+    reads = [reads[i] for i in order]
+    fa, fq, idx = str(tmp_path / "ref.fa"), str(tmp_path / "reads.fq"), str(tmp_path / "idx")
+    synth.write_fasta(fa, records)
+    synth.write_fastq(fq, reads)
+    subprocess.run([FEM_BINARY, "index", "12", "3", fa, idx], check=True, stderr=subprocess.DEVNULL)
+    o = ol.Oracle(fasta=fa)
+    o.load_index(idx)
+    o.set_params(3, 1)
+
+    def both(fq_path, tag, **kw):
+        want_sam, got_sam = str(tmp_path / (tag + ".want.sam")), str(tmp_path / (tag + ".sam"))
+        st = o.map_file(fq_path, want_sam)
+        counters = run_fem_map(fa, idx, fq_path, got_sam, 3, 1, **kw)
+        assert counters == st.as_tuple()[:5]
+        with open(want_sam, "rb") as f, open(got_sam, "rb") as g:
+            assert g.read() == f.read(), tag
+        return counters
+
+    c = both(fq, "mixed", threads=6, extra=("--batch", "257"))
+    assert c[1] > 500 and c[4] > 5000
+    both(fq, "mixed_one_batch", threads=2)
+    one = str(tmp_path / "one.fq")
+    synth.write_fastq(one, reads[:1])
+    both(one, "one")
+    empty = str(tmp_path / "empty.fq")
+    open(empty, "wb").close()
+    want_sam, got_sam = str(tmp_path / "empty.want.sam"), str(tmp_path / "empty.sam")
+    p = subprocess.run([FEM_BINARY, "map", "-e", "3", "-t", "2", "--ref", fa, "--index", idx, "--read1", empty, "-o", got_sam],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert p.returncode == 0, p.stderr[-1000:]
+    with open(got_sam, "rb") as g:
+        body = g.read()
+    assert body.count(b"\n") == len(records) and all(line.startswith(b"@SQ") for line in body.splitlines())  # src/output_queue.c:93-116
+    o.close()
