@@ -178,24 +178,30 @@ struct CompactArgs {
   uint32_t *map_rs;             // owning read-strand of each record (k_trace)
 };
 
+// Eight lanes per read-strand, four read-strands per warp: most read-strands hold one or two candidates (a
+// warp each was 2 M nearly empty warps per 1 M reads, 384 us), the repeat-rich ones thousands (eight at a time).
+#define COMPACT_LPR 8u
 __global__ void __launch_bounds__(256) k_compact(CompactArgs A) {
-  const uint32_t lane = lane_id();
-  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (rs >= A.n_rs || A.rs_map_count[rs] == 0) return;
-  const uint64_t cf = A.rs_cand_first[rs], mf = A.rs_map_first[rs];
-  const uint32_t n = A.rs_cand_count[rs];
+  const uint32_t lane = lane_id(), sub = lane & (COMPACT_LPR - 1), grp = lane / COMPACT_LPR;
+  const uint64_t rs = ((uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32u / COMPACT_LPR) + grp;
+  const bool live = rs < A.n_rs && A.rs_map_count[rs] != 0;
+  uint64_t cf = 0, mf = 0;
+  uint32_t n = 0;
+  if (live) { cf = A.rs_cand_first[rs]; mf = A.rs_map_first[rs]; n = A.rs_cand_count[rs]; }
+  const uint32_t n_max = __reduce_max_sync(0xffffffffu, n);
+  const uint32_t below = (1u << sub) - 1u;
   uint32_t w = 0;
-  for (uint32_t base = 0; base < n; base += 32) {
-    const uint32_t t = base + lane;
+  for (uint32_t base = 0; base < n_max; base += COMPACT_LPR) {
+    const uint32_t t = base + sub;
     uint32_t r = 0xFFFFFFFFu;
     if (t < n) r = A.result[cf + t];
-    const uint32_t m = __ballot_sync(0xffffffffu, r != 0xFFFFFFFFu);
+    const uint32_t m = (__ballot_sync(0xffffffffu, r != 0xFFFFFFFFu) >> (COMPACT_LPR * grp)) & ((1u << COMPACT_LPR) - 1u);
     if (r != 0xFFFFFFFFu) {
       ulonglong2 rec;
       rec.x = A.cand[cf + t];
       // {int32 end_offset, uint8 direction, uint8 edit_distance, 2 reserved} little endian
       rec.y = (uint64_t)(r & 0xFFFFu) | ((uint64_t)(rs & 1) << 32) | ((uint64_t)(r >> 16) << 40);
-      const uint64_t o = mf + w + __popc(m & lanemask_lt());
+      const uint64_t o = mf + w + __popc(m & below);
       A.maps[o] = rec;
       A.map_rs[o] = (uint32_t)rs;
     }

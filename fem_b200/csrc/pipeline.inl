@@ -392,7 +392,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     pa.n_rs = (uint32_t)n_rs;
     pa.maps = s.maps.as<ulonglong2>();
     pa.map_rs = s.map_rs.as<uint32_t>();
-    k_compact<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(pa);
+    k_compact<<<(unsigned)((n_rs + 31) / 32), 256, 0, s.stream>>>(pa); // 8 warps x (32 / COMPACT_LPR) read-strands
     ++s.n_launches;
     CU(cudaGetLastError());
   }
