@@ -141,9 +141,9 @@ __device__ __forceinline__ uint32_t sam_emit_read(const SamArgs &A, uint32_t i, 
     }
   const uint64_t off = A.read_off[i];
   const uint32_t l = (uint32_t)(A.read_off[i + 1] - off);
-  const char *name = A.names + A.name_off[i];
-  uint32_t name_l = 0;
-  while (name[name_l]) ++name_l;
+  const uint64_t name_at = A.name_off[i];
+  const char *name = A.names + name_at;
+  const uint32_t name_l = (uint32_t)(A.name_off[i + 1] - name_at) - 1u; // names lie back to back, one NUL after each
   SamOut<MODE> o;
   o.p = p;
   o.n = 0;
@@ -302,9 +302,9 @@ __global__ void __launch_bounds__(128) k_sam_big_len(SamArgs A) {
     }
     const uint64_t off = A.read_off[i];
     const uint32_t l = (uint32_t)(A.read_off[i + 1] - off);
-    const char *name = A.names + A.name_off[i];
-    uint32_t name_l = 0;
-    while (name[name_l]) ++name_l;
+    const uint64_t name_at = A.name_off[i];
+    const char *name = A.names + name_at;
+    const uint32_t name_l = (uint32_t)(A.name_off[i + 1] - name_at) - 1u; // names lie back to back, one NUL after each
     uint32_t running = 0;
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {
       const uint32_t r = r0 + lane;
@@ -349,9 +349,9 @@ __global__ void __launch_bounds__(128) k_sam_big_write(SamArgs A) {
     const uint32_t n = (uint32_t)(A.rs_map_first[2ull * i + 2] - m0);
     const uint64_t off = A.read_off[i];
     const uint32_t l = (uint32_t)(A.read_off[i + 1] - off);
-    const char *name = A.names + A.name_off[i];
-    uint32_t name_l = 0;
-    while (name[name_l]) ++name_l;
+    const uint64_t name_at = A.name_off[i];
+    const char *name = A.names + name_at;
+    const uint32_t name_l = (uint32_t)(A.name_off[i + 1] - name_at) - 1u; // names lie back to back, one NUL after each
     const uint64_t t_read = A.text_off[i];
     const uint32_t read_len = (uint32_t)(A.text_off[i + 1] - t_read);
     for (uint32_t r0 = 0; r0 < n; r0 += 32) {

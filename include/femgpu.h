@@ -108,7 +108,8 @@ typedef struct {
 } femgpu_result;
 
 /* What the SAM records need beyond the bases (src/align.c:546-632 reads them from the kseq record):
- * names[name_off[i]..] NUL terminated; quals share the batch's offsets, has_qual[i] == 0 prints '*'.
+ * name i = names[name_off[i] .. name_off[i+1] - 1) followed by one NUL (back to back, as kseq's name.s
+ * copied with its terminator); quals share the batch's offsets, has_qual[i] == 0 prints '*'.
  * Host memory, valid until the submit returns. */
 typedef struct {
   const char *names;
