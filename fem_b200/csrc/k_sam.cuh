@@ -174,23 +174,29 @@ __global__ void __launch_bounds__(128) k_sam_len(SamArgs A) {
   A.read_bytes[i] = sam_emit_read<0>(A, i, m0, n, nullptr, nullptr, nullptr);
 }
 
-// len bytes of src[at..] into shared memory, by the warp: each lane takes four bytes out of two aligned
-// words (the buffers are padded past their last byte, slot_reserve)
-__device__ __forceinline__ void sam_copy_field(char *dst, const char *src, uint64_t at, uint32_t len, uint32_t lane) {
+// len bytes of src[at..] into shared memory by one lane: aligned words, shifted into place (the buffers
+// are padded past their last byte, slot_reserve).  Every lane of the warp copies its own read's field, so
+// all lanes work (a warp-wide copy of one 100-byte field keeps 25 of them busy for one round).
+__device__ __forceinline__ void sam_copy_own(char *dst, const char *src, uint64_t at, uint32_t len) {
   const uint32_t *w = reinterpret_cast<const uint32_t *>(src + (at & ~3ull));
   const uint32_t sh = (uint32_t)(at & 3u) * 8u;
-  for (uint32_t k = lane * 4u; k < len; k += 128u) {
-    const uint32_t v = __funnelshift_r(w[k >> 2], w[(k >> 2) + 1], sh);
-    dst[k] = (char)v;
-    if (k + 1 < len) dst[k + 1] = (char)(v >> 8);
-    if (k + 2 < len) dst[k + 2] = (char)(v >> 16);
-    if (k + 3 < len) dst[k + 3] = (char)(v >> 24);
+  uint32_t prev = w[0];
+  uint32_t k = 0;
+  for (; k + 4 <= len; k += 4) {
+    const uint32_t next = w[(k >> 2) + 1];
+    const uint32_t v = __funnelshift_r(prev, next, sh);
+    prev = next;
+    dst[k] = (char)v; dst[k + 1] = (char)(v >> 8); dst[k + 2] = (char)(v >> 16); dst[k + 3] = (char)(v >> 24);
+  }
+  if (k < len) {
+    const uint32_t v = __funnelshift_r(prev, w[(k >> 2) + 1], sh);
+    for (uint32_t j = 0; k + j < len; ++j) dst[k + j] = (char)(v >> (8 * j));
   }
 }
 
 // pass 2: the text.  The 32 reads of a warp own one contiguous span of the output (text_off is the scan
 // of their sizes): each lane builds its read's records in the warp's shared-memory image of that span,
-// the warp copies SEQ and QUAL of each read into it with coalesced loads, and the image goes out as
+// SEQ and QUAL included (word-wise copies), and the image goes out as
 // 16-byte stores (the image starts at the span's offset within its 16-byte line, so both sides are
 // aligned alike).  Spans larger than `image` bytes are written byte-wise straight to global memory.
 __global__ void __launch_bounds__(128) k_sam_write(SamArgs A, uint32_t image) {
@@ -229,14 +235,9 @@ __global__ void __launch_bounds__(128) k_sam_write(SamArgs A, uint32_t image) {
     l = (uint32_t)(A.read_off[i + 1] - roff);
   }
   __syncwarp();
-  for (uint32_t r = 0; r < 32u; ++r) {
-    const uint32_t sp = __shfl_sync(0xFFFFFFFFu, seq_at, r);
-    if (sp == 0xFFFFFFFFu) continue;
-    const uint32_t rl = __shfl_sync(0xFFFFFFFFu, l, r);
-    const uint64_t ro = __shfl_sync(0xFFFFFFFFu, roff, r);
-    const bool wq = __shfl_sync(0xFFFFFFFFu, (int)with_qual, r) != 0;
-    sam_copy_field(img + sp, A.bases, ro, rl, lane);
-    if (wq) sam_copy_field(img + sp + rl + 1, A.quals, ro, rl, lane);
+  if (seq_at != 0xFFFFFFFFu) { // SEQ and QUAL of this lane's read
+    sam_copy_own(img + seq_at, A.bases, roff, l);
+    if (with_qual) sam_copy_own(img + seq_at + l + 1, A.quals, roff, l);
   }
   __syncwarp();
   char *dst = A.text + (t0 - skew); // 16-byte aligned (the text buffer is)
