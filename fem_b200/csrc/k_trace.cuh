@@ -11,7 +11,7 @@
 // flagged FEMGPU_ALN_HOST and the host runs its own femhost_alignment on them.
 #pragma once
 #include "common.cuh"
-#include "k_verify.cuh" // ref_code_at
+#include "k_verify.cuh" // RefCursor
 
 #define ALN_MAX_OPS 18
 #define ALN_HOST 0xFFu // n_cigar value: not computed on the device
@@ -61,14 +61,14 @@ template <bool HAS_N>
 __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t *text, const uint16_t *cig, int nc, uint32_t *dst) {
   char md[48];
   int o = 0, tp = 0;
-  uint32_t run = 0, w2 = 0, wn = 0; // the reference is walked forward: 16 bases per loaded word
-  bool fresh = true;
+  uint32_t run = 0;
+  RefCursor<HAS_N> ref; // the reference is walked forward
+  ref.seek(R, gref);
   for (int ci = 0; ci < nc; ++ci) {
     const uint32_t op = cig[ci] & 3u, len = cig[ci] >> 2;
     if (op == 0) {
-      for (uint32_t j = 0; j < len; ++j, ++gref, ++tp) {
-        const uint32_t c = ref_code_at<HAS_N>(R, gref, w2, wn, fresh);
-        fresh = false;
+      for (uint32_t j = 0; j < len; ++j, ++tp) {
+        const uint32_t c = ref.next();
         if (c == text[tp]) { ++run; continue; }
         if (run) { o = md_put_uint(md, o, run); run = 0; }
         if (o < 48) md[o] = "ACGTN"[c];
@@ -80,9 +80,8 @@ __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t
       if (run) { o = md_put_uint(md, o, run); run = 0; }
       if (o < 48) md[o] = '^';
       ++o;
-      for (uint32_t j = 0; j < len; ++j, ++gref) {
-        const uint32_t c = ref_code_at<HAS_N>(R, gref, w2, wn, fresh);
-        fresh = false;
+      for (uint32_t j = 0; j < len; ++j) {
+        const uint32_t c = ref.next();
         if (o < 48) md[o] = "ACGTN"[c];
         ++o;
       }
@@ -117,14 +116,12 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   if (!A.ref_canonical || (A.read_flags[read] & 1u) || l > LCAP || l <= 0 || start < 0) { aln_store(out, 0, ALN_HOST, cig); return; }
   const uint8_t *text = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
   const uint64_t g0 = A.ref.rec_base[rec.x >> 32] + (uint32_t)rec.x; // window[0]
-  uint32_t w2 = 0, wn = 0;
+  RefCursor<HAS_N> ref;
 
   // :289-300 plain comparison at the reported end; no difference -> lM
   int diff = 0;
-  {
-    uint64_t g = g0 + (uint64_t)start;
-    for (int i = 0; i < l; ++i, ++g) diff += text[i] != ref_code_at<HAS_N>(A.ref, g, w2, wn, i == 0);
-  }
+  ref.seek(A.ref, g0 + (uint64_t)start);
+  for (int i = 0; i < l; ++i) diff += text[i] != ref.next();
   if (diff == 0) {
     cig[0] = (uint16_t)(l << 2);
     char md[48]; // no difference: the MD text is the read length
@@ -143,14 +140,14 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   uint32_t hist[LCAP];
   {
     uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0, VP = 0, VN = 0;
-    uint64_t g = g0;
-    for (int i = 0; i < 2 * e; ++i, ++g) {
-      const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, i == 0), bit = 1u << i;
+    ref.seek(A.ref, g0);
+    for (int i = 0; i < 2 * e; ++i) {
+      const uint32_t c = ref.next(), bit = 1u << i;
       p0 |= c == 0 ? bit : 0u; p1 |= c == 1 ? bit : 0u; p2 |= c == 2 ? bit : 0u; p3 |= c == 3 ? bit : 0u; p4 |= c == 4 ? bit : 0u;
     }
     const uint32_t hi = 1u << (2 * e);
-    for (int i = 0; i < l; ++i, ++g) {
-      const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, e == 0 && i == 0);
+    for (int i = 0; i < l; ++i) {
+      const uint32_t c = ref.next();
       p0 |= c == 0 ? hi : 0u; p1 |= c == 1 ? hi : 0u; p2 |= c == 2 ? hi : 0u; p3 |= c == 3 ? hi : 0u; p4 |= c == 4 ? hi : 0u;
       const uint32_t t = text[i];
       const uint32_t eq = t == 0 ? p0 : t == 1 ? p1 : t == 2 ? p2 : t == 3 ? p3 : p4;

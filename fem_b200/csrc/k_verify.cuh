@@ -38,6 +38,39 @@ __device__ __forceinline__ uint32_t ref_code_at(const DevRef &R, uint64_t g, uin
   return c;
 }
 
+// The same codes for a forward walk over the reference: the current words are kept shifted down, so a base
+// costs an AND, a shift and a counter (the random-access form above spends more on 64-bit index arithmetic
+// than on the base).  Reads one word past the walk's last base at most (the arrays are padded).
+template <bool HAS_N>
+struct RefCursor {
+  const uint32_t *p2, *pn;
+  uint32_t w2, wn;
+  int left2, leftn;
+  __device__ __forceinline__ void seek(const DevRef &R, uint64_t g) {
+    const uint32_t s2 = (uint32_t)g & 15u;
+    p2 = R.ref2 + (g >> 4);
+    w2 = __ldg(p2) >> (2u * s2);
+    left2 = 16 - (int)s2;
+    if (HAS_N) {
+      const uint32_t sn = (uint32_t)g & 31u;
+      pn = R.refn + (g >> 5);
+      wn = __ldg(pn) >> sn;
+      leftn = 32 - (int)sn;
+    }
+  }
+  __device__ __forceinline__ uint32_t next() {
+    uint32_t c = w2 & 3u;
+    w2 >>= 2;
+    if (--left2 == 0) { w2 = __ldg(++p2); left2 = 16; }
+    if (HAS_N) {
+      if (wn & 1u) c = 4u;
+      wn >>= 1;
+      if (--leftn == 0) { wn = __ldg(++pn); leftn = 32; }
+    }
+    return c;
+  }
+};
+
 template <bool HAS_N>
 __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
   const uint64_t ci = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -50,13 +83,13 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
   const int l = (int)(A.read_off[read + 1] - off);
   const uint8_t *text = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
   const uint64_t cand = A.cand[ci];
-  uint64_t g = A.ref.rec_base[cand >> 32] + (uint32_t)cand;
   const int e = A.e;
-  uint32_t w2 = 0, wn = 0;
+  RefCursor<HAS_N> ref;
+  ref.seek(A.ref, A.ref.rec_base[cand >> 32] + (uint32_t)cand);
 
   uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0; // Peq rows
-  for (int i = 0; i < 2 * e; ++i, ++g) {           // align.c:104-107
-    const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, i == 0);
+  for (int i = 0; i < 2 * e; ++i) {                // align.c:104-107
+    const uint32_t c = ref.next();
     const uint32_t bit = 1u << i;
     p0 |= c == 0 ? bit : 0u; p1 |= c == 1 ? bit : 0u; p2 |= c == 2 ? bit : 0u;
     p3 |= c == 3 ? bit : 0u; p4 |= c == 4 ? bit : 0u;
@@ -65,8 +98,8 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
   uint32_t VP = 0, VN = 0;
   int err = 0, cols = l;
   bool dead = false;
-  for (int i = 0; i < l; ++i, ++g) {               // align.c:117-134
-    const uint32_t c = ref_code_at<HAS_N>(A.ref, g, w2, wn, e == 0 && i == 0);
+  for (int i = 0; i < l; ++i) {                    // align.c:117-134
+    const uint32_t c = ref.next();
     p0 |= c == 0 ? hi : 0u; p1 |= c == 1 ? hi : 0u; p2 |= c == 2 ? hi : 0u;
     p3 |= c == 3 ? hi : 0u; p4 |= c == 4 ? hi : 0u;
     const uint32_t t = text[i];
