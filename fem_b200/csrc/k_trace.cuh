@@ -98,6 +98,67 @@ __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t
   return (uint32_t)o;
 }
 
+// ---- reads and references without N: 16 bases per word ---------------------------------------------------
+// 16 reference bases from g on / 16 read bases from t on (tw: the read packed like ref2, one spare word)
+__device__ __forceinline__ uint32_t ref_word_at(const DevRef &R, uint64_t g) {
+  const uint32_t *p = R.ref2 + (g >> 4);
+  return __funnelshift_r(__ldg(p), __ldg(p + 1), 2u * ((uint32_t)g & 15u));
+}
+__device__ __forceinline__ uint32_t text_word_at(const uint32_t *tw, int t) {
+  return __funnelshift_r(tw[t >> 4], tw[(t >> 4) + 1], 2u * ((uint32_t)t & 15u));
+}
+
+// md_build_store for an N-free reference and read: mismatches of a match run are found 16 bases at a time
+// (XOR of the packed words), so the cost follows the number of differences, not the read length
+__device__ uint32_t md_build_store_packed(const DevRef &R, uint64_t gref, const uint32_t *tw, const uint16_t *cig, int nc, uint32_t *dst) {
+  char md[48];
+  int o = 0, tp = 0;
+  uint32_t run = 0;
+  for (int ci = 0; ci < nc; ++ci) {
+    const uint32_t op = cig[ci] & 3u, len = cig[ci] >> 2;
+    if (op == 0) {
+      uint32_t pos = 0; // bases of this run already accounted for
+      for (uint32_t j0 = 0; j0 < len; j0 += 16) {
+        const uint32_t rw = ref_word_at(R, gref + j0), x = rw ^ text_word_at(tw, tp + (int)j0), n = min(16u, len - j0);
+        uint32_t mm = (x | (x >> 1)) & 0x55555555u;
+        if (n < 16u) mm &= (1u << (2u * n)) - 1u;
+        while (mm) {
+          const uint32_t b = (uint32_t)__ffs((int)mm) - 1u, j = j0 + (b >> 1);
+          mm &= mm - 1u;
+          run += j - pos;
+          pos = j + 1;
+          if (run) { o = md_put_uint(md, o, run); run = 0; }
+          if (o < 48) md[o] = "ACGT"[(rw >> b) & 3u];
+          ++o;
+        }
+      }
+      run += len - pos;
+      gref += len;
+      tp += (int)len;
+    } else if (op == 1) {
+      tp += (int)len;
+    } else {
+      if (run) { o = md_put_uint(md, o, run); run = 0; }
+      if (o < 48) md[o] = '^';
+      ++o;
+      for (uint32_t j = 0; j < len; ++j) {
+        if (o < 48) md[o] = "ACGT"[ref_word_at(R, gref + j) & 3u];
+        ++o;
+      }
+      gref += len;
+    }
+    if (o > ALN_MD_MAX) return ALN_HOST;
+  }
+  if (run) o = md_put_uint(md, o, run);
+  if (o > ALN_MD_MAX) return ALN_HOST;
+  for (int i = o; i < 48; ++i) md[i] = 0;
+#pragma unroll
+  for (int w = 0; w < 12; ++w)
+    dst[w] = (uint32_t)(uint8_t)md[4 * w] | ((uint32_t)(uint8_t)md[4 * w + 1] << 8) | ((uint32_t)(uint8_t)md[4 * w + 2] << 16) |
+             ((uint32_t)(uint8_t)md[4 * w + 3] << 24);
+  return (uint32_t)o;
+}
+
 template <bool HAS_N, int LCAP>
 __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   const uint64_t mi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -118,10 +179,39 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   const uint64_t g0 = A.ref.rec_base[rec.x >> 32] + (uint32_t)rec.x; // window[0]
   RefCursor<HAS_N> ref;
 
+  // the read 2 bits per base, as the reference is stored; packed = neither holds an N (every comparison
+  // below is then a word-wise XOR)
+  uint32_t tw[(LCAP + 15) / 16 + 1];
+  bool packed = !HAS_N;
+  if (!HAS_N) {
+    uint32_t any4 = 0;
+    for (int w = 0; w * 16 < l; ++w) {
+      uint32_t v = 0;
+      const int n = min(16, l - w * 16);
+      for (int j = 0; j < n; ++j) {
+        const uint32_t c = text[w * 16 + j];
+        any4 |= c;
+        v |= (c & 3u) << (2 * j);
+      }
+      tw[w] = v;
+    }
+    tw[(l + 15) / 16] = 0;
+    packed = (any4 & 4u) == 0;
+  }
+
   // :289-300 plain comparison at the reported end; no difference -> lM
   int diff = 0;
-  ref.seek(A.ref, g0 + (uint64_t)start);
-  for (int i = 0; i < l; ++i) diff += text[i] != ref.next();
+  if (packed) {
+    const uint64_t gs = g0 + (uint64_t)start;
+    for (int t = 0; t < l; t += 16) {
+      uint32_t x = ref_word_at(A.ref, gs + (uint64_t)t) ^ text_word_at(tw, t);
+      if (l - t < 16) x &= (1u << (2 * (l - t))) - 1u;
+      diff |= x != 0;
+    }
+  } else {
+    ref.seek(A.ref, g0 + (uint64_t)start);
+    for (int i = 0; i < l; ++i) diff += text[i] != ref.next();
+  }
   if (diff == 0) {
     cig[0] = (uint16_t)(l << 2);
     char md[48]; // no difference: the MD text is the read length
@@ -208,5 +298,7 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   if (fail || n_ops - first + 1 > ALN_MAX_OPS) { aln_store(out, 0, ALN_HOST, cig); return; }
   int nc = 0;
   for (int i = n_ops; i >= first; --i) cig[nc++] = (uint16_t)(((uint32_t)cnt[i] << 2) | ops[i]);
-  aln_store(out, start, (uint32_t)nc, cig, md_build_store<HAS_N>(A.ref, g0 + (uint64_t)start, text, cig, nc, out + 10));
+  const uint32_t md_len = packed ? md_build_store_packed(A.ref, g0 + (uint64_t)start, tw, cig, nc, out + 10)
+                                 : md_build_store<HAS_N>(A.ref, g0 + (uint64_t)start, text, cig, nc, out + 10);
+  aln_store(out, start, (uint32_t)nc, cig, md_len);
 }
