@@ -210,6 +210,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   cudaGetDeviceProperties(&prop, device);
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
+  if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
   for (auto &s : c->slot) {
     if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
       set_error(FEMGPU_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError()));

@@ -40,17 +40,24 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   // one lane per group pays Q*W serial steps, the warp scan pays step*Q*ceil(W/32) rounds of ~7x the cost
   pl->lane_dp = c->seed_dp_mode == 1 ? 1 : c->seed_dp_mode == 2 ? 0 : pl->w_max <= 8 * pl->step;
   pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4; // 4 warps
-  // several read-strands per warp where the lane form leaves most lanes idle (k_seed_multi.cuh)
+  // several read-strands per warp where the lane form leaves most lanes idle (k_seed_multi.cuh).  Automatic
+  // choice: only while the lookup table stays in L2 (k <= 12, 67 MB; with k = 14 its gathers go to HBM and the
+  // one-read-strand form's larger number of warps in flight wins: cfg5 10 ms against 22 ms) and while the
+  // regions of 32/step read-strands are small enough for ten blocks per SM (each warp works through its
+  // read-strands one after the other, so it needs many neighbours), and only for the shapes it was measured
+  // to win on -- reads of up to 128 bases (one round of base coding per read-strand) with at most 7 seeds per
+  // group: cfg2 2.1 against 2.9 ms, cfg1 0.20 against 0.29 ms per 1 M / 0.1 M reads; on cfg3 (150 bases, 9 seeds per
+  // group) it is bound by the shared-memory pipe (ncu: short-scoreboard and MIO-throttle stalls) at 6.2 against
+  // 3.7 ms, so the one-read-strand form stays there.
   pl->seed_R = 0;
-  // (automatic choice: only while the lookup table is small enough to stay in L2 -- k <= 12, 67 MB; with
-  //  k = 14 its gathers go to HBM and the one-read-strand form's larger number of warps in flight wins:
-  //  cfg5 10 ms against 22 ms)
-  if (((c->seed_dp_mode == 0 && pl->k <= 12) || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
+  if ((c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
     pl->seed_words_per_rs = seed_multi_words_per_rs(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step);
     int R = 32 / pl->step;
-    while (R > 1 && 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH) > 56 * 1024) --R;
-    const size_t bytes = 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH);
-    if (bytes <= c->smem_optin) { pl->seed_R = R; pl->seed_smem = bytes; }
+    size_t bytes = 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH);
+    bool use = c->seed_dp_mode == 3 || (pl->k <= 12 && bytes <= 24 * 1024 && pl->l_max <= 128 && pl->Q <= 7);
+    if (c->seed_dp_mode == 3)
+      while (R > 1 && bytes > 56 * 1024) { --R; bytes = 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH); }
+    if (use && bytes <= c->smem_optin) { pl->seed_R = R; pl->seed_smem = bytes; }
   }
   pl->cand_smem = (size_t)4 * (c->sort_capacity + c->acc_capacity) * 8;
   // hash path: room for 4x the expected location-list total of a group on a uniform index
