@@ -369,7 +369,7 @@ def run_ours(args):
 
     # ---- end-to-end leg: the whole `FEM map` run through the C ABI, host buffers -----------------
     cores = cpu_cores()
-    threads = args.e2e_threads or max(1, cores // world - 3)
+    threads = args.e2e_threads or max(2, cores // world - 3)  # -t; the engine adds its readers, GPU threads and copiers
     out = ("/dev/shm" if os.path.isdir("/dev/shm") else args.data_dir) + "/fem_bench_r%d.sam" % rank
     e2e_steps = args.e2e_steps or args.steps
     hm.map_file(fq, out, w["e"], w["a"], threads=threads, batch_reads=args.e2e_batch)  # warm-up: pinned staging buffers, page cache

@@ -26,6 +26,7 @@ static int stage_batch(femgpu_ctx *c, Slot &s, const femgpu_params *p, const fem
     return set_error(FEMGPU_EINVAL, "shared-memory plan too large (seed %zu, cand %zu bytes)", pl->seed_smem, pl->cand_smem);
   TRY(slot_reserve(c, s, *pl, b->n_reads, n_bases));
   s.params = *p;
+  s.blocking_sync = c->blocking_sync != 0;
   s.n_reads = b->n_reads;
   s.n_bases = n_bases;
   s.l_max = l_max;
@@ -161,7 +162,7 @@ static int fetch_result(Slot &s, femgpu_result *r) {
     CU(cudaMemcpyAsync(s.h_status.p, s.rs_status.p, 2ull * n, cudaMemcpyDeviceToHost, s.stream));
   }
   cudaEventRecord(s.ev[5], s.stream);
-  CU(cudaStreamSynchronize(s.stream));
+  CU(slot_sync(s));
   uint64_t mapped = 0, infeasible = 0;
   const uint8_t *st = s.h_status.as<uint8_t>();
   for (uint32_t i = 0; i < n; ++i) {
@@ -295,7 +296,7 @@ extern "C" int femgpu_candidates_batch(femgpu_ctx *c, const femgpu_params *p, co
     CU(cudaMemcpyAsync(s.h_before.p, s.rs_before.p, n_rs * 4, cudaMemcpyDeviceToHost, s.stream));
     CU(cudaMemcpyAsync(s.h_status.p, s.rs_status.p, n_rs, cudaMemcpyDeviceToHost, s.stream));
   }
-  CU(cudaStreamSynchronize(s.stream));
+  CU(slot_sync(s));
   out->first = hfirst;
   out->cands = hfirst + n_rs + 1;
   out->before = s.h_before.as<uint32_t>();
@@ -334,7 +335,7 @@ extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_st
   TRY(run_verify_and_compact(c, s, pl));
   TRY(run_sam(c, s)); // the batch's names and qualities are still resident when it was submitted with SAM inputs
   cudaEventRecord(s.ev[7], s.stream);
-  CU(cudaStreamSynchronize(s.stream));
+  CU(slot_sync(s));
   float t;
   if (ms_stage)
   {

@@ -114,6 +114,8 @@ struct Counters {
 struct Slot {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[8] = {};
+  cudaEvent_t ev_block = nullptr; // cudaEventBlockingSync: slot_sync
+  bool blocking_sync = false;     // copied from the context with every batch
   // inputs / per read-strand state
   DBuf bases, read_off, codes, rs_status, rs_before, rs_max_f, rs_sum_f;
   DBuf seed_begin, seed_freq, seed_start;
@@ -150,6 +152,13 @@ struct Slot {
   uint64_t cols_executed = 0;
 };
 
+// wait for the slot's stream: spinning (lowest latency) or asleep on an event (leaves the core to the other threads)
+static inline cudaError_t slot_sync(Slot &s) {
+  if (!s.blocking_sync || !s.ev_block) return cudaStreamSynchronize(s.stream);
+  cudaError_t e = cudaEventRecord(s.ev_block, s.stream);
+  return e != cudaSuccess ? e : cudaEventSynchronize(s.ev_block);
+}
+
 struct femgpu_ctx {
   int device = 0;
   int sm_count = 0;
@@ -181,6 +190,7 @@ struct femgpu_ctx {
   uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
+  int blocking_sync = 0; // host waits sleep on an event instead of spinning in cudaStreamSynchronize (small hosts, one process per GPU)
   int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan, 3 several read-strands per warp (tests force each)
   Slot slot[2];
   int last_slot = 0;
@@ -210,6 +220,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   cudaGetDeviceProperties(&prop, device);
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
+  if (const char *b = getenv("FEM_BLOCKING_SYNC")) c->blocking_sync = atoi(b) != 0;
   if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
   for (auto &s : c->slot) {
     if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -218,6 +229,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
       return nullptr;
     }
     for (auto &e : s.ev) cudaEventCreate(&e);
+    cudaEventCreateWithFlags(&s.ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
   }
   return c;
 }
@@ -233,6 +245,7 @@ static void slot_release(Slot &s) {
   HBuf *h[] = {&s.h_sam_text, &s.h_sam_off, &s.h_sam_host, &s.h_aln, &s.h_counters, &s.h_first, &s.h_maps, &s.h_overflow, &s.h_plan, &s.h_cands, &s.h_before, &s.h_status};
   for (auto *b : h) b->release();
   for (auto &e : s.ev) if (e) cudaEventDestroy(e);
+  if (s.ev_block) cudaEventDestroy(s.ev_block);
   if (s.stream) cudaStreamDestroy(s.stream);
 }
 
@@ -259,6 +272,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
   else if (k == "device_traceback") c->device_traceback = value != 0;
+  else if (k == "blocking_sync" && (value == 0 || value == 1)) c->blocking_sync = (int)value;
   else if (k == "seed_dp_mode" && value >= 0 && value <= 3) c->seed_dp_mode = (int)value;
   else return set_error(FEMGPU_EINVAL, "unknown option or bad value: %s=%lld", key, (long long)value);
   return 0;

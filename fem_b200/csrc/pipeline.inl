@@ -151,7 +151,7 @@ __global__ void k_gather_u32(const uint32_t *src, const uint32_t *idx, uint32_t 
 
 static int read_counters(Slot &s, Counters *out) {
   CU(cudaMemcpyAsync(s.h_counters.p, s.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s.stream));
-  CU(cudaStreamSynchronize(s.stream));
+  CU(slot_sync(s));
   *out = *s.h_counters.as<Counters>();
   return 0;
 }
@@ -269,7 +269,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
       const uint32_t n_over = hc.overflow_count;
       TRY(s.h_overflow.reserve((size_t)n_over * 4));
       CU(cudaMemcpyAsync(s.h_overflow.p, s.overflow_list.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
-      CU(cudaStreamSynchronize(s.stream));
+      CU(slot_sync(s));
       const uint32_t *ol = s.h_overflow.as<uint32_t>();
       std::vector<uint32_t> order(ol, ol + n_over);
       std::sort(order.begin(), order.end()); // deterministic processing order
@@ -284,7 +284,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
       s.n_launches += 2;
       CU(cudaMemcpyAsync(s.h_plan.p, s.big_S.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
       CU(cudaMemcpyAsync(s.h_plan.as<uint32_t>() + n_over, s.big_A.p, (size_t)n_over * 4, cudaMemcpyDeviceToHost, s.stream));
-      CU(cudaStreamSynchronize(s.stream));
+      CU(slot_sync(s));
       const uint32_t *mx = s.h_plan.as<uint32_t>(), *sm = mx + n_over;
       const uint64_t limit_elems = (uint64_t)c->scratch_limit_bytes / 8;
       uint32_t done = 0;

@@ -739,7 +739,8 @@ static int parallel_readable(const char *path, uint64_t *size) {
   return n == 2 && b[0] == '@';
 }
 
-#define N_PAR_READERS 4
+#define N_PAR_READERS 4 /* at most; -t of them on small hosts (one process per GPU leaves each a few cores) */
+static int par_readers(int n_threads) { const char *e = getenv("FEM_READERS"); const int n = e ? atoi(e) : n_threads; return n < 1 ? 1 : n > N_PAR_READERS ? N_PAR_READERS : n; }
 /* threads that copy finished text into the output file: the page cache's per-file locks stop scaling
  * beyond about six (measured on tmpfs: 7.5 GB/s from six threads, the same from sixteen at three times the CPU time) */
 #define MAX_COPIERS 6
@@ -764,12 +765,17 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     if (r.chunk_bytes < 4096) r.chunk_bytes = 4096;
     r.n_chunks = 0;
     while (par_range_start(&r, r.n_chunks) < r.file_size) ++r.n_chunks;
-    r.readers_left = N_PAR_READERS;
+    r.readers_left = par_readers(opt->n_threads);
   } else {
     r.rd = femhost_reader_open(reads_path);
     if (!r.rd) return -1;
   }
   r.device_sam = !(getenv("FEM_DEVICE_SAM") && atoi(getenv("FEM_DEVICE_SAM")) == 0);
+  /* few host threads (one process per GPU on a small host): the two GPU threads sleep while they wait instead of
+   * spinning on cores the readers and copiers need (four cores, -t 2: 13.7 -> 14.4 M reads/s on cfg2) */
+  if (!getenv("FEM_BLOCKING_SYNC"))
+    for (int g = 0; g < m->n_gpus; ++g) femgpu_set_option(m->ctx[g], "blocking_sync", opt->n_threads <= 3);
+
   r.out_fd = -1;
   if (sam_path) {
     r.out_fd = open(sam_path, O_RDWR | O_CREAT | O_TRUNC, 0644);
@@ -791,7 +797,7 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   const double t_start = femhost_now();
   r.t_start = t_start;
   r.trace = getenv("FEM_TRACE") && atoi(getenv("FEM_TRACE")) != 0;
-  const int n_gpu_threads = 2 * m->n_gpus, n_format = opt->n_threads, n_readers = parallel ? N_PAR_READERS : 1;
+  const int n_gpu_threads = 2 * m->n_gpus, n_format = opt->n_threads, n_readers = parallel ? par_readers(opt->n_threads) : 1;
   const int n_copiers = opt->n_threads < max_copiers() ? opt->n_threads : max_copiers(), n_workers = n_format + n_copiers;
   r.n_batches = (size_t)(2 * n_gpu_threads + 6 + (parallel ? N_PAR_READERS : 0));
   if (m->n_pool != r.n_batches) {

@@ -139,7 +139,8 @@ const char *femgpu_last_error(void);
 void *femgpu_alloc_pinned(size_t bytes);
 void femgpu_free_pinned(void *p);
 
-/* Tunables (all optional): "scratch_limit_bytes", "arena_candidates", "sort_capacity",
+/* Tunables (all optional): "blocking_sync" (1: host waits sleep on an event instead of spinning; for hosts
+ * with few cores per GPU), "scratch_limit_bytes", "arena_candidates", "sort_capacity",
  * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan, 3 lane per group with several read-strands per warp),
  * "cand_mode" (0 automatic: near-pair path when a >= 1, hash path when a = 0; 1 sort path only;
  * 2 hash path first; 3 near-pair path first; 4 all-groups-at-once path first, the automatic
