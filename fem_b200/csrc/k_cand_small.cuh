@@ -2,35 +2,52 @@
 // all groups of a read-strand at once, one warp per read-strand.
 //
 // Same result as k_cand / k_cand_hash / k_cand_pair and therefore as src/filter.c:45-144.  When the
-// location lists of ALL step x Q selected seeds of a read-strand together hold at most SMALL_CAP
-// entries, the per-group machinery of the other paths (tables, bitmaps, one dependent round of loads
-// per group) costs more than the work itself.  Here
+// location lists of ALL step x Q selected seeds of a read-strand together hold at most CAP entries,
+// the per-group machinery of the other paths (tables, bitmaps, one dependent round of loads per
+// group) costs more than the work itself.  Here
 //   gather   every lane takes seeds lane, lane + 32, ... and copies their shifted occurrences into one
 //            shared-memory array (all groups' loads in flight together: one round trip to HBM);
 //   F5       the lane that owns a group's last (most frequent) seed drops that seed's entries above
-//            the maximum of the group's other entries (src/filter.c:85), or the whole group when the
+//            the maximum of the group's other entries (src/filter.c:85), or all of them when the
 //            other seeds contribute nothing;
 //   exact    one lane per entry counts the entries of the same group in [x, x+e] (itself included):
 //            x survives additional_qgram_filter (src/filter.c:118-131) iff that count exceeds a;
-//            repeated values keep their first copy only;
+//            repeated values keep their first copy only.  The count runs on the low 32 bits first
+//            (an upper bound of the exact count); only entries that pass it are counted in 64 bits;
 //   merge    survivors are rank-sorted by (group, value) and folded group by group into the running
-//            list with the greedy "> last + e" rule (src/filter.c:45-78) by one lane.
+//            list with the greedy "> last + e" rule (src/filter.c:45-78) by one lane;
+//   emit     remove_out_ranged_candidates (src/filter.c:133-144) in one ballot (the list holds <= 32).
 // Read-strands with more entries, seeds or survivors than the buffers hold go to k_cand (sort based)
 // through the overflow list.
+//
+// Two shapes: R = 1 (step x Q <= 32 seeds: one seed per lane, cfg1 and cfg2; 2.1 KB of shared memory
+// per warp) and R = 4 (up to 128 seeds, cfg5).
 #pragma once
 #include "common.cuh"
 #include "k_cand.cuh"
 
-#define SMALL_CAP 256u   // entries per read-strand
-#define SMALL_SEEDS 128u // step * Q
-#define SMALL_SC 64u     // survivors per read-strand
-#define SMALL_AC 32u     // running candidate list
+template <int R> struct SmallShape {
+  static constexpr uint32_t SEEDS = 32u * R;              // step * Q
+  static constexpr uint32_t CAP = R == 1 ? 128u : 256u;   // entries per read-strand
+  static constexpr uint32_t SC = R == 1 ? 32u : 64u;      // survivors per read-strand
+  static constexpr uint32_t AC = R == 1 ? 16u : 32u;      // running candidate list (<= 32: emit is one ballot)
+  __host__ __device__ static constexpr size_t bytes_per_warp() {
+    return ((size_t)CAP * 8 + (SC + 2 * AC) * 8 + SEEDS * 8 + (SEEDS + 1) * 4 + SC + CAP + 15) & ~(size_t)15;
+  }
+};
+#define SMALL_SEEDS_MAX 128u
+#define SMALL_CAP_NARROW 128u
 
-__host__ __device__ inline size_t cand_small_smem_bytes_per_warp() {
-  return (size_t)SMALL_CAP * 8 + (SMALL_SC + 2 * SMALL_AC) * 8 + (SMALL_SEEDS + 1) * 4 + SMALL_SEEDS * 8 + SMALL_SC + 64 + SMALL_CAP + 12;
+__device__ __forceinline__ void small_hand_on(const CandArgs &A, uint64_t rs, uint32_t lane) {
+  if (lane == 0) {
+    A.overflow_list[atomicAdd(A.overflow_count, 1u)] = (uint32_t)rs;
+    A.rs_cand_first[rs] = 0;
+    A.rs_cand_count[rs] = 0;
+  }
 }
 
-__global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
+template <int R> __global__ void __launch_bounds__(128, R == 1 ? 12 : 8) k_cand_small(CandArgs A, uint32_t inv_Q) {
+  typedef SmallShape<R> Sh;
   extern __shared__ uint64_t smem_small[];
   const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
   const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
@@ -39,34 +56,37 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
     if (lane == 0) { A.rs_cand_first[rs] = 0; A.rs_cand_count[rs] = 0; }
     return;
   }
-  unsigned char *base = reinterpret_cast<unsigned char *>(smem_small) + (size_t)wib * ((cand_small_smem_bytes_per_warp() + 15) & ~(size_t)15);
-  uint64_t *vals = reinterpret_cast<uint64_t *>(base);       // [SMALL_CAP] shifted occurrences, FEM_SENTINEL = dropped
-  uint64_t *sv = vals + SMALL_CAP;                            // [SMALL_SC] survivors
-  uint64_t *acc = sv + SMALL_SC, *acc2 = acc + SMALL_AC;
-  uint64_t *smax = acc2 + SMALL_AC;                           // [SMALL_SEEDS] largest kept entry per seed (FEM_SENTINEL: none)
-  uint32_t *eo = reinterpret_cast<uint32_t *>(smax + SMALL_SEEDS); // [SMALL_SEEDS + 1] entry offsets of the seeds
-  uint8_t *sg = reinterpret_cast<uint8_t *>(eo + SMALL_SEEDS + 1); // [SMALL_SC] group of each survivor
-  uint8_t *dead = sg + SMALL_SC;                              // [64] group contributes nothing
-  uint8_t *eg = dead + 64;                                    // [SMALL_CAP] group of each entry
-  const uint32_t Q = (uint32_t)A.Q, step = (uint32_t)A.step, S = Q * step;
+  // read length for the range filter: requested now, used at the very end
+  const uint32_t read = (uint32_t)(rs >> 1);
+  const uint64_t ro0 = A.read_off[read], ro1 = A.read_off[read + 1];
+  unsigned char *base = reinterpret_cast<unsigned char *>(smem_small) + (size_t)wib * Sh::bytes_per_warp();
+  uint64_t *vals = reinterpret_cast<uint64_t *>(base);       // [CAP] shifted occurrences, FEM_SENTINEL = dropped
+  uint64_t *sv = vals + Sh::CAP;                              // [SC] survivors
+  uint64_t *acc = sv + Sh::SC, *acc2 = acc + Sh::AC;
+  uint64_t *smax = acc2 + Sh::AC;                             // [SEEDS] largest kept entry per seed (FEM_SENTINEL: none)
+  uint32_t *eo = reinterpret_cast<uint32_t *>(smax + Sh::SEEDS); // [SEEDS + 1] entry offsets of the seeds
+  uint8_t *sg = reinterpret_cast<uint8_t *>(eo + Sh::SEEDS + 1); // [SC] group of each survivor
+  uint8_t *eg = sg + Sh::SC;                                  // [CAP] group of each entry
+  const uint32_t Q = (uint32_t)A.Q, S = Q * (uint32_t)A.step;
   const uint32_t a = (uint32_t)A.a;
+  const uint32_t e32 = (uint32_t)A.e;
   const uint64_t e = (uint64_t)A.e;
-  bool overflow = S > SMALL_SEEDS || step > 64;
+  if (S > Sh::SEEDS) { small_hand_on(A, rs, lane); return; }
 
   // ---- gather: seeds lane, lane + 32, ... ; exclusive prefix of the frequencies over all seeds ------
   uint32_t T = 0;
-  if (!overflow) {
-    const size_t so = (size_t)rs * S;
-    uint32_t sb[4], sf[4], sst[4];
+  const size_t so = (size_t)rs * S;
+  uint32_t sb[R], sf[R], sst[R], off[R];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const uint32_t s = lane + 32u * r;
-      sb[r] = 0; sf[r] = 0; sst[r] = 0;
-      if (s < S) { sb[r] = A.seed_begin[so + s]; sf[r] = A.seed_freq[so + s]; sst[r] = A.seed_start[so + s]; }
-    }
-    uint32_t off[4];
+  for (int r = 0; r < R; ++r) {
+    const uint32_t s = lane + 32u * r;
+    sb[r] = 0; sf[r] = 0; sst[r] = 0;
+    if (s < S) { sb[r] = A.seed_begin[so + s]; sf[r] = A.seed_freq[so + s]; sst[r] = A.seed_start[so + s]; }
+  }
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+  for (int r = 0; r < R; ++r) {
+    off[r] = T;
+    if (32u * r < S) { // uniform
       uint32_t incl = sf[r];
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -76,66 +96,63 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
       off[r] = T + incl - sf[r];
       T += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (T > SMALL_CAP) overflow = true;
-    else {
-      // the first two entries of every seed are requested before any is used: one round trip for
-      // almost all of them on a sparse index
-      uint64_t o0[4], o1[4];
+  }
+  if (T > Sh::CAP) { small_hand_on(A, rs, lane); return; }
+  {
+    // the first two entries of every seed are requested before any is used: one round trip for
+    // almost all of them on a sparse index
+    uint64_t o0[R], o1[R];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        o0[r] = 0; o1[r] = 0;
-        if (sf[r] > 0) o0[r] = A.occ[(uint64_t)sb[r]];
-        if (sf[r] > 1) o1[r] = A.occ[(uint64_t)sb[r] + 1];
+    for (int r = 0; r < R; ++r) {
+      o0[r] = 0; o1[r] = 0;
+      if (sf[r] > 0) o0[r] = A.occ[(uint64_t)sb[r]];
+      if (sf[r] > 1) o1[r] = A.occ[(uint64_t)sb[r] + 1];
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t s = lane + 32u * r;
+      if (s < S) {
+        eo[s] = off[r];
+        const uint8_t g = (uint8_t)(Q == 1 ? s : __umulhi(s, inv_Q)); // s / Q
+        uint64_t mx = FEM_SENTINEL;
+        for (uint32_t k = 0; k < sf[r]; ++k) {
+          const uint64_t o = k == 0 ? o0[r] : k == 1 ? o1[r] : A.occ[(uint64_t)sb[r] + k];
+          uint64_t v = FEM_SENTINEL;
+          if ((uint32_t)o >= sst[r]) { v = o - sst[r]; mx = v; } // filter.c:89,106; the run ascends
+          vals[off[r] + k] = v;
+          eg[off[r] + k] = g;
+        }
+        smax[s] = mx;
       }
+    }
+    if (lane == 0) eo[S] = T;
+  }
+  __syncwarp();
+  // ---- F5: the last seed of a group only contributes entries up to the largest entry of the others; the
+  //      lane that holds the last seed finds that bound and drops its own entries above it
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const uint32_t s = lane + 32u * r;
-        if (s < S) {
-          eo[s] = off[r];
-          const uint8_t g = (uint8_t)(s / Q);
-          uint64_t mx = FEM_SENTINEL;
-          for (uint32_t k = 0; k < sf[r]; ++k) {
-            const uint64_t o = k == 0 ? o0[r] : k == 1 ? o1[r] : A.occ[(uint64_t)sb[r] + k];
-            uint64_t v = FEM_SENTINEL;
-            if ((uint32_t)o >= sst[r]) { v = o - sst[r]; mx = v; } // filter.c:89,106; the run ascends
-            vals[off[r] + k] = v;
-            eg[off[r] + k] = g;
-          }
-          smax[s] = mx;
+  for (int r = 0; r < R; ++r) {
+    const uint32_t s = lane + 32u * r;
+    if (s < S) {
+      const uint32_t g = Q == 1 ? s : __umulhi(s, inv_Q);
+      if (s == g * Q + Q - 1 && sf[r]) {
+        uint64_t mv = 0;
+        bool has = false;
+        for (uint32_t i = s + 1 - Q; i < s; ++i) {
+          const uint64_t m = smax[i];
+          if (m != FEM_SENTINEL && (!has || m > mv)) { mv = m; has = true; }
+        }
+        for (uint32_t k = 0; k < sf[r]; ++k) {
+          const uint64_t v = vals[off[r] + k];
+          if (!has || (v != FEM_SENTINEL && v > mv)) vals[off[r] + k] = FEM_SENTINEL;
         }
       }
-      if (lane == 0) eo[S] = T;
     }
-  }
-  if (overflow) {
-    if (lane == 0) {
-      A.overflow_list[atomicAdd(A.overflow_count, 1u)] = (uint32_t)rs;
-      A.rs_cand_first[rs] = 0;
-      A.rs_cand_count[rs] = 0;
-    }
-    return;
-  }
-  __syncwarp();
-  // ---- F5: the last seed of a group only contributes entries up to the largest entry of the others: one
-  //      lane per group finds that bound (kept in sv, free until the count), one lane per entry applies it
-  for (uint32_t g = lane; g < step; g += 32) {
-    uint64_t mv = 0;
-    bool has = false;
-    for (uint32_t i = 0; i + 1 < Q; ++i) {
-      const uint64_t m = smax[g * Q + i];
-      if (m != FEM_SENTINEL && (!has || m > mv)) { mv = m; has = true; }
-    }
-    dead[g] = has ? 0 : 1;
-    sv[g] = mv;
-  }
-  __syncwarp();
-  for (uint32_t t = lane; t < T; t += 32) {
-    const uint32_t g = eg[t];
-    if (t >= eo[g * Q + Q - 1] && (dead[g] || (vals[t] != FEM_SENTINEL && vals[t] > sv[g]))) vals[t] = FEM_SENTINEL;
   }
   __syncwarp();
   // ---- exact: one lane per entry ---------------------------------------------------------------------
   uint32_t ns = 0;
+  const uint32_t *vals_lo = reinterpret_cast<const uint32_t *>(vals); // little endian: word 2j = low half of vals[j]
   for (uint32_t t0 = 0; t0 < T; t0 += 32) {
     const uint32_t t = t0 + lane;
     bool keep = false;
@@ -144,42 +161,49 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
     if (t < T) {
       x = vals[t];
       g = eg[t];
-      if (x != FEM_SENTINEL && !dead[g]) {
+      if (x != FEM_SENTINEL) {
         const uint32_t gs = eo[g * Q], ge = eo[g * Q + Q];
-        uint32_t cnt = 0;
-        bool dup = false;
-        for (uint32_t j = gs; j < ge; ++j) {
-          const uint64_t y = vals[j];
-          cnt += (y - x <= e) ? 1u : 0u;        // FEM_SENTINEL - x is far above e
-          dup = dup || (y == x && j < t);
+        // low halves first: y - x <= e in 64 bits implies it in 32 bits, so this count bounds the exact one
+        const uint32_t xl = (uint32_t)x;
+        uint32_t c32 = 0;
+#pragma unroll 2
+        for (uint32_t j = gs; j < ge; ++j) c32 += (vals_lo[2 * j] - xl <= e32) ? 1u : 0u;
+        if (c32 > a) {
+          uint32_t cnt = 0;
+          bool dup = false;
+          for (uint32_t j = gs; j < ge; ++j) {
+            const uint64_t y = vals[j];
+            cnt += (y - x <= e) ? 1u : 0u;        // FEM_SENTINEL - x is far above e
+            dup = dup || (y == x && j < t);
+          }
+          keep = cnt > a && !dup;
         }
-        keep = cnt > a && !dup;
       }
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, keep);
     if (keep) {
       const uint32_t k = ns + __popc(bal & lanemask_lt());
-      if (k < SMALL_SC) { sv[k] = x; sg[k] = (uint8_t)g; }
+      if (k < Sh::SC) { sv[k] = x; sg[k] = (uint8_t)g; }
     }
     ns += __popc(bal);
   }
-  if (ns > SMALL_SC) {
-    if (lane == 0) {
-      A.overflow_list[atomicAdd(A.overflow_count, 1u)] = (uint32_t)rs;
-      A.rs_cand_first[rs] = 0;
-      A.rs_cand_count[rs] = 0;
-    }
+  if (ns > Sh::SC) { small_hand_on(A, rs, lane); return; }
+  if (ns == 0) { // nothing survives: no candidates (the usual case for the strand the read did not come from)
+    if (lane == 0) { A.rs_cand_first[rs] = 0; A.rs_cand_count[rs] = 0; }
     return;
   }
   __syncwarp();
   // ---- survivors in (group, value) order, then the groups folded one after the other -----------------
   uint32_t na = 0;
-  bool too_long = false;
-  if (ns) {
-    uint64_t x[2];
-    uint32_t g[2], rank[2];
+  if (ns == 1) {
+    if (lane == 0) acc[0] = sv[0];
+    na = 1;
+  } else {
+    bool too_long = false;
+    uint64_t x[Sh::SC / 32];
+    uint32_t g[Sh::SC / 32], rank[Sh::SC / 32];
 #pragma unroll
-    for (int r = 0; r < 2; ++r) {
+    for (int r = 0; r < (int)(Sh::SC / 32); ++r) {
       const uint32_t i = lane + 32u * r;
       x[r] = 0; g[r] = 0; rank[r] = 0;
       if (i < ns) {
@@ -192,7 +216,7 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
     }
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < 2; ++r)
+    for (int r = 0; r < (int)(Sh::SC / 32); ++r)
       if (lane + 32u * r < ns) { sv[rank[r]] = x[r]; sg[rank[r]] = (uint8_t)g[r]; }
     __syncwarp();
     if (lane == 0) {
@@ -208,12 +232,12 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
           if (i1 < na && (i2 >= end || acc[i1] < sv[i2])) v = acc[i1++];
           else v = sv[i2++];
           if (no == 0 || v > last + e) {
-            if (no < SMALL_AC) acc2[no] = v;
+            if (no < Sh::AC) acc2[no] = v;
             ++no;
             last = v;
           }
         }
-        if (no > SMALL_AC) { too_long = true; break; }
+        if (no > Sh::AC) { too_long = true; break; }
         na = no;
         uint64_t *sw = acc; acc = acc2; acc2 = sw;
       }
@@ -221,17 +245,35 @@ __global__ void __launch_bounds__(128) k_cand_small(CandArgs A) {
     too_long = __shfl_sync(0xffffffffu, (int)too_long, 0) != 0;
     na = __shfl_sync(0xffffffffu, na, 0);
     // lane 0 may have swapped the two lists an odd number of times
-    const uint32_t swapped = __shfl_sync(0xffffffffu, (uint32_t)(acc != sv + SMALL_SC), 0);
-    acc = swapped ? sv + SMALL_SC + SMALL_AC : sv + SMALL_SC;
-  }
-  if (too_long) {
-    if (lane == 0) {
-      A.overflow_list[atomicAdd(A.overflow_count, 1u)] = (uint32_t)rs;
-      A.rs_cand_first[rs] = 0;
-      A.rs_cand_count[rs] = 0;
-    }
-    return;
+    const uint32_t swapped = __shfl_sync(0xffffffffu, (uint32_t)(acc != sv + Sh::SC), 0);
+    acc = swapped ? sv + Sh::SC + Sh::AC : sv + Sh::SC;
+    if (too_long) { small_hand_on(A, rs, lane); return; }
   }
   __syncwarp();
-  rs_emit_candidates(A, rs, lane, acc, na);
+  // ---- emit: the range filter and the arena slice (same outputs as rs_emit_candidates; na <= 32) ------
+  {
+    const uint32_t l = (uint32_t)(ro1 - ro0);
+    bool keep = false;
+    uint64_t v = 0;
+    if (lane < na) {
+      v = acc[lane];
+      const uint32_t pos = (uint32_t)v, len = A.rec_len[v >> 32];
+      keep = pos >= e32 && pos + l + e32 < len;
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, keep);
+    const uint32_t n_keep = __popc(m);
+    unsigned long long first = 0;
+    if (lane == 0 && n_keep) first = atomicAdd(A.cand_count, (unsigned long long)n_keep);
+    first = __shfl_sync(0xffffffffu, first, 0);
+    if (n_keep && first + n_keep > A.cand_cap) {
+      if (lane == 0) { *A.error_flag = 1; A.rs_cand_first[rs] = 0; A.rs_cand_count[rs] = 0; }
+      return;
+    }
+    if (keep) {
+      const uint64_t o = first + __popc(m & lanemask_lt());
+      A.cand[o] = v - e; // the stored candidate is the band's left edge
+      A.cand_rs[o] = (uint32_t)rs;
+    }
+    if (lane == 0) { A.rs_cand_first[rs] = first; A.rs_cand_count[rs] = n_keep; }
+  }
 }

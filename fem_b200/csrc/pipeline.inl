@@ -14,6 +14,8 @@ struct Plan { // derived from params + the batch
   bool pair32;
   int first_path; // 0 sort, 1 hash, 2 pair, 3 small
   size_t small_smem;
+  int small_R;          // k_cand_small shape: 1 (one seed per lane) or 4
+  uint32_t small_inv_Q; // multiply-high reciprocal of Q for seed -> group
 };
 
 static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
@@ -90,11 +92,15 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     pl->pair32 = c->occ32_ok && c->pair_layout == 32;
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
-  pl->small_smem = 4 * ((cand_small_smem_bytes_per_warp() + 15) & ~(size_t)15);
   {
     // sparse index: all groups of a read-strand at once when their lists are expected to hold < 100 entries
     const double per_rs = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q * pl->step;
-    const bool fits = (uint32_t)(pl->Q * pl->step) <= SMALL_SEEDS && pl->step <= 64;
+    const bool fits = (uint32_t)(pl->Q * pl->step) <= SMALL_SEEDS_MAX;
+    const bool narrow = (uint32_t)(pl->Q * pl->step) <= 32u && per_rs <= 0.5 * SMALL_CAP_NARROW;
+    pl->small_R = c->small_shape == 4 ? 4 : c->small_shape == 1 ? ((uint32_t)(pl->Q * pl->step) <= 32u ? 1 : 4) : (narrow ? 1 : 4);
+    pl->small_smem = 4 * (pl->small_R == 1 ? SmallShape<1>::bytes_per_warp() : SmallShape<4>::bytes_per_warp());
+    if (c->small_shape == 9) { pl->small_R = 9; pl->small_smem = 4 * ((cand_small_v1_smem_bytes_per_warp() + 15) & ~(size_t)15); }
+    pl->small_inv_Q = pl->Q > 1 ? (uint32_t)(0x100000000ull / (uint64_t)pl->Q) + 1u : 0u;
     if (c->cand_mode == 4 || (c->cand_mode == 0 && fits && per_rs <= 100.0)) pl->first_path = 3;
     if (c->cand_mode == 3 && pl->a < 1) pl->first_path = 1;
   }
@@ -229,7 +235,6 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
-  if (pl.small_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.small_smem));
   if (pl.pair32_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair32_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
 
@@ -241,7 +246,9 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand_cap = s.cand_cap;
     ca.rs_list = nullptr;
     ca.n_list = 0;
-    if (pl.first_path == 3) k_cand_small<<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca);
+    if (pl.first_path == 3 && pl.small_R == 1) k_cand_small<1><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
+    else if (pl.first_path == 3 && pl.small_R == 9) k_cand_small_v1<<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca);
+    else if (pl.first_path == 3) k_cand_small<4><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
     else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
     else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);

@@ -134,14 +134,18 @@ def test_candidates_pair_path_sizes(setup, bits, values, layout):
         setup.mapper.set_option("cand_mode", 0)
 
 
-def test_candidates_small_path(setup):
+@pytest.mark.parametrize("shape", [0, 1, 4])
+def test_candidates_small_path(setup, shape):
     """k_cand_small (all groups of a read-strand at once) forced on every case: dense cases hand most
-    read-strands on to the sort path, sparse ones stay."""
+    read-strands on to the sort path, sparse ones stay.  Shape 1: one seed per lane (at most 32 seeds,
+    128 entries; wider cases take shape 4), 4: up to 128 seeds and 256 entries, 0: the automatic choice."""
     seqs = [r[1] for r in setup.reads]
     setup.mapper.set_option("cand_mode", 4)
+    setup.mapper.set_option("small_shape", shape)
     try:
         check_candidates(setup, seqs)
     finally:
+        setup.mapper.set_option("small_shape", 0)
         setup.mapper.set_option("cand_mode", 0)
 
 
