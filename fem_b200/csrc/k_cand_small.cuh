@@ -63,7 +63,7 @@ template <int R> __global__ void __launch_bounds__(128, R == 1 ? 12 : 8) k_cand_
   uint64_t *vals = reinterpret_cast<uint64_t *>(base);       // [CAP] shifted occurrences, FEM_SENTINEL = dropped
   uint64_t *sv = vals + Sh::CAP;                              // [SC] survivors
   uint64_t *acc = sv + Sh::SC, *acc2 = acc + Sh::AC;
-  uint64_t *smax = acc2 + Sh::AC;                             // [SEEDS] largest kept entry per seed (FEM_SENTINEL: none)
+  uint64_t *smax = acc2 + Sh::AC;                             // [SEEDS] largest kept entry per seed + 1 (0: none); shape 4 only
   uint32_t *eo = reinterpret_cast<uint32_t *>(smax + Sh::SEEDS); // [SEEDS + 1] entry offsets of the seeds
   uint8_t *sg = reinterpret_cast<uint8_t *>(eo + Sh::SEEDS + 1); // [SC] group of each survivor
   uint8_t *eg = sg + Sh::SC;                                  // [CAP] group of each entry
@@ -98,6 +98,8 @@ template <int R> __global__ void __launch_bounds__(128, R == 1 ? 12 : 8) k_cand_
     }
   }
   if (T > Sh::CAP) { small_hand_on(A, rs, lane); return; }
+  // largest kept entry of each seed plus one (0: none), for F5
+  uint64_t mxp[R];
   {
     // the first two entries of every seed are requested before any is used: one round trip for
     // almost all of them on a sparse index
@@ -111,40 +113,87 @@ template <int R> __global__ void __launch_bounds__(128, R == 1 ? 12 : 8) k_cand_
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const uint32_t s = lane + 32u * r;
+      mxp[r] = 0;
       if (s < S) {
         eo[s] = off[r];
         const uint8_t g = (uint8_t)(Q == 1 ? s : __umulhi(s, inv_Q)); // s / Q
-        uint64_t mx = FEM_SENTINEL;
-        for (uint32_t k = 0; k < sf[r]; ++k) {
-          const uint64_t o = k == 0 ? o0[r] : k == 1 ? o1[r] : A.occ[(uint64_t)sb[r] + k];
+        const uint32_t p = off[r];
+        if (sf[r] > 0) {
           uint64_t v = FEM_SENTINEL;
-          if ((uint32_t)o >= sst[r]) { v = o - sst[r]; mx = v; } // filter.c:89,106; the run ascends
-          vals[off[r] + k] = v;
-          eg[off[r] + k] = g;
+          if ((uint32_t)o0[r] >= sst[r]) { v = o0[r] - sst[r]; mxp[r] = v + 1; } // filter.c:89,106; the run ascends
+          vals[p] = v;
+          eg[p] = g;
         }
-        smax[s] = mx;
+        if (sf[r] > 1) {
+          uint64_t v = FEM_SENTINEL;
+          if ((uint32_t)o1[r] >= sst[r]) { v = o1[r] - sst[r]; mxp[r] = v + 1; }
+          vals[p + 1] = v;
+          eg[p + 1] = g;
+        }
+        for (uint32_t k = 2; k < sf[r]; ++k) {
+          const uint64_t o = A.occ[(uint64_t)sb[r] + k];
+          uint64_t v = FEM_SENTINEL;
+          if ((uint32_t)o >= sst[r]) { v = o - sst[r]; mxp[r] = v + 1; }
+          vals[p + k] = v;
+          eg[p + k] = g;
+        }
+        if (R != 1) smax[s] = mxp[r];
       }
     }
     if (lane == 0) eo[S] = T;
   }
-  __syncwarp();
   // ---- F5: the last seed of a group only contributes entries up to the largest entry of the others; the
-  //      lane that holds the last seed finds that bound and drops its own entries above it
-#pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const uint32_t s = lane + 32u * r;
-    if (s < S) {
+  //      lane that holds the last seed drops its own entries above that bound (the run ascends: walk back
+  //      from its end to the first entry that stays)
+  if (R == 1) {
+    // one seed per lane: maximum over the Q - 1 lanes below by a sliding window of shuffles (windows of the
+    // lanes that hold a group's last seed lie inside their group)
+    const uint32_t W = Q - 1;
+    uint64_t w = 0;
+    if (W) {
+      w = __shfl_up_sync(0xffffffffu, mxp[0], 1);
+      if (lane < 1) w = 0;
+      uint32_t win = 1;
+      while (2 * win <= W) {
+        uint64_t t = __shfl_up_sync(0xffffffffu, w, win);
+        if (lane < win) t = 0;
+        w = max(w, t);
+        win *= 2;
+      }
+      if (win < W) {
+        const uint32_t d = W - win;
+        uint64_t t = __shfl_up_sync(0xffffffffu, w, d);
+        if (lane < d) t = 0;
+        w = max(w, t);
+      }
+    }
+    const uint32_t s = lane;
+    if (s < S && sf[0]) {
       const uint32_t g = Q == 1 ? s : __umulhi(s, inv_Q);
-      if (s == g * Q + Q - 1 && sf[r]) {
-        uint64_t mv = 0;
-        bool has = false;
-        for (uint32_t i = s + 1 - Q; i < s; ++i) {
-          const uint64_t m = smax[i];
-          if (m != FEM_SENTINEL && (!has || m > mv)) { mv = m; has = true; }
+      if (s == g * Q + Q - 1)
+        for (uint32_t k = sf[0]; k-- > 0;) {
+          const uint64_t v = vals[off[0] + k];
+          if (v == FEM_SENTINEL) continue;
+          if (v < w) break; // v <= bound, w = bound + 1 (0: no bound, nothing stays)
+          vals[off[0] + k] = FEM_SENTINEL;
         }
-        for (uint32_t k = 0; k < sf[r]; ++k) {
-          const uint64_t v = vals[off[r] + k];
-          if (!has || (v != FEM_SENTINEL && v > mv)) vals[off[r] + k] = FEM_SENTINEL;
+    }
+  } else {
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t s = lane + 32u * r;
+      if (s < S && sf[r]) {
+        const uint32_t g = Q == 1 ? s : __umulhi(s, inv_Q);
+        if (s == g * Q + Q - 1) {
+          uint64_t w = 0;
+          for (uint32_t i = s + 1 - Q; i < s; ++i) w = max(w, smax[i]);
+          for (uint32_t k = sf[r]; k-- > 0;) {
+            const uint64_t v = vals[off[r] + k];
+            if (v == FEM_SENTINEL) continue;
+            if (v < w) break;
+            vals[off[r] + k] = FEM_SENTINEL;
+          }
         }
       }
     }
