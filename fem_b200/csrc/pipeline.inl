@@ -93,7 +93,8 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
   {
-    // sparse index: all groups of a read-strand at once when their lists are expected to hold < 100 entries
+    // sparse index: all groups of a read-strand at once when their lists are expected to hold <= 128 entries
+    // (expectation over random q-grams; the DP picks the rarest, cfg5: 104 expected, 47 found)
     const double per_rs = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q * pl->step;
     const bool fits = (uint32_t)(pl->Q * pl->step) <= SMALL_SEEDS_MAX;
     const bool narrow = (uint32_t)(pl->Q * pl->step) <= 32u && per_rs <= 0.5 * SMALL_CAP_NARROW;
@@ -101,7 +102,7 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     pl->small_smem = 4 * (pl->small_R == 1 ? SmallShape<1>::bytes_per_warp() : SmallShape<4>::bytes_per_warp());
     if (c->small_shape == 9) { pl->small_R = 9; pl->small_smem = 4 * ((cand_small_v1_smem_bytes_per_warp() + 15) & ~(size_t)15); }
     pl->small_inv_Q = pl->Q > 1 ? (uint32_t)(0x100000000ull / (uint64_t)pl->Q) + 1u : 0u;
-    if (c->cand_mode == 4 || (c->cand_mode == 0 && fits && per_rs <= 100.0)) pl->first_path = 3;
+    if (c->cand_mode == 4 || (c->cand_mode == 0 && fits && per_rs <= 128.0)) pl->first_path = 3;
     if (c->cand_mode == 3 && pl->a < 1) pl->first_path = 1;
   }
   return 0;
