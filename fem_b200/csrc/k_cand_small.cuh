@@ -12,9 +12,8 @@
 //            other seeds contribute nothing;
 //   exact    one lane per entry counts the entries of the same group in [x, x+e] (itself included):
 //            x survives additional_qgram_filter (src/filter.c:118-131) iff that count exceeds a;
-//            repeated values keep their first copy only.  Whole groups go side by side through windows of
-//            32 entries; with a >= 1 two match.any over hashed (group, 16-wide bucket) keys pick the few
-//            entries that have a neighbour at all, and only those are counted;
+//            repeated values keep their first copy only.  The count runs on the low 32 bits first
+//            (an upper bound of the exact count); only entries that pass it are counted in 64 bits;
 //   merge    survivors are rank-sorted by (group, value) and folded group by group into the running
 //            list with the greedy "> last + e" rule (src/filter.c:45-78) by one lane;
 //   emit     remove_out_ranged_candidates (src/filter.c:133-144) in one ballot (the list holds <= 32).
@@ -200,59 +199,42 @@ template <int R> __global__ void __launch_bounds__(128, R == 1 ? 12 : 8) k_cand_
     }
   }
   __syncwarp();
-  // ---- exact: one lane per entry, whole groups side by side in a window of at most 32 entries -----------
-  // With a >= 1 an entry needs ANOTHER entry of its group within e <= 7: the two then share a 16-wide bucket
-  // of the grid at offset 0 or of the grid at offset 8, so two match.any over hashed (group, bucket) keys
-  // find every entry that can survive (and a few by hash collision); only those run the exact count.
+  // ---- exact: one lane per entry ---------------------------------------------------------------------
   uint32_t ns = 0;
-  const bool prefilter = a >= 1 && e32 <= 7;
-  const uint32_t n_groups = (uint32_t)A.step;
-  for (uint32_t g0 = 0; g0 < n_groups;) {
-    const uint32_t first = eo[g0 * Q];
-    uint32_t g1 = g0 + 1, end = eo[g1 * Q];
-    while (g1 < n_groups) { // further whole groups while the window holds them
-      const uint32_t nx = eo[(g1 + 1) * Q];
-      if (nx - first > 32) break;
-      end = nx;
-      ++g1;
-    }
-    const bool one_trip = end - first <= 32; // otherwise group g0 alone is longer: plain trips over it
-    for (uint32_t t0 = first; t0 < end; t0 += 32) {
-      const uint32_t t = t0 + lane;
-      uint64_t x = FEM_SENTINEL;
-      uint32_t g = 0;
-      if (t < end) { x = vals[t]; g = eg[t]; }
-      const bool live = x != FEM_SENTINEL;
-      bool check = live;
-      if (prefilter && one_trip) {
-        const uint64_t b0 = x >> 4, b1 = (x + 8) >> 4; // live values are far below the sentinel
-        const uint32_t gk = g * 0x85EBCA6Bu;
-        const uint32_t k0 = live ? ((uint32_t)b0 ^ ((uint32_t)(b0 >> 32) * 0x9E3779B1u)) + gk : ~lane;
-        const uint32_t k1 = live ? ((uint32_t)b1 ^ ((uint32_t)(b1 >> 32) * 0x9E3779B1u)) + gk : ~lane;
-        const uint32_t lm = __ballot_sync(0xffffffffu, live);
-        const uint32_t m = (__match_any_sync(0xffffffffu, k0) | __match_any_sync(0xffffffffu, k1)) & lm & ~(1u << lane);
-        check = live && m != 0;
-      }
-      bool keep = false;
-      if (check) {
+  const uint32_t *vals_lo = reinterpret_cast<const uint32_t *>(vals); // little endian: word 2j = low half of vals[j]
+  for (uint32_t t0 = 0; t0 < T; t0 += 32) {
+    const uint32_t t = t0 + lane;
+    bool keep = false;
+    uint64_t x = FEM_SENTINEL;
+    uint32_t g = 0;
+    if (t < T) {
+      x = vals[t];
+      g = eg[t];
+      if (x != FEM_SENTINEL) {
         const uint32_t gs = eo[g * Q], ge = eo[g * Q + Q];
-        uint32_t cnt = 0;
-        bool dup = false;
-        for (uint32_t j = gs; j < ge; ++j) {
-          const uint64_t y = vals[j];
-          cnt += (y - x <= e) ? 1u : 0u;        // FEM_SENTINEL - x is far above e
-          dup = dup || (y == x && j < t);
+        // low halves first: y - x <= e in 64 bits implies it in 32 bits, so this count bounds the exact one
+        const uint32_t xl = (uint32_t)x;
+        uint32_t c32 = 0;
+#pragma unroll 2
+        for (uint32_t j = gs; j < ge; ++j) c32 += (vals_lo[2 * j] - xl <= e32) ? 1u : 0u;
+        if (c32 > a) {
+          uint32_t cnt = 0;
+          bool dup = false;
+          for (uint32_t j = gs; j < ge; ++j) {
+            const uint64_t y = vals[j];
+            cnt += (y - x <= e) ? 1u : 0u;        // FEM_SENTINEL - x is far above e
+            dup = dup || (y == x && j < t);
+          }
+          keep = cnt > a && !dup;
         }
-        keep = cnt > a && !dup;
       }
-      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-      if (keep) {
-        const uint32_t k = ns + __popc(bal & lanemask_lt());
-        if (k < Sh::SC) { sv[k] = x; sg[k] = (uint8_t)g; }
-      }
-      ns += __popc(bal);
     }
-    g0 = g1;
+    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      const uint32_t k = ns + __popc(bal & lanemask_lt());
+      if (k < Sh::SC) { sv[k] = x; sg[k] = (uint8_t)g; }
+    }
+    ns += __popc(bal);
   }
   if (ns > Sh::SC) { small_hand_on(A, rs, lane); return; }
   if (ns == 0) { // nothing survives: no candidates (the usual case for the strand the read did not come from)

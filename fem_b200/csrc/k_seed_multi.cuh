@@ -36,7 +36,7 @@ __host__ __device__ inline uint32_t seed_multi_words_per_rs(int n_words_max, int
 }
 #define SEED_MULTI_SCRATCH 64u // words per warp after the regions: per-lane DP minimum and failure flag
 
-__global__ void __launch_bounds__(128) k_seed_multi(SeedMultiArgs B) {
+__global__ void __launch_bounds__(128, 10) k_seed_multi(SeedMultiArgs B) {
   extern __shared__ __align__(16) uint32_t smem_seed_multi[];
   const SeedArgs &A = B.a;
   const uint32_t lane = lane_id(), warp_in_block = threadIdx.x >> 5;
@@ -74,6 +74,93 @@ __global__ void __launch_bounds__(128) k_seed_multi(SeedMultiArgs B) {
     }
   };
   fetch(0, 0, cur);
+  if (!(R & 1)) {
+    // Both strands of a read at once (R even: a warp's read-strands are whole reads).  The characters are
+    // read and decoded once; the reverse strand's codes are stored mirrored, its ambiguity count comes from
+    // the same ballot, and its packed words are the forward words read backwards: a 16-base window of the
+    // forward stream, 2-bit groups reversed (brev + swap of neighbouring bits), complemented.  Ambiguous
+    // bases (hashed as A on both strands, utils.h:95-100) are cleared afterwards where a read has any.
+    for (int q = 0; 2 * q < n_here; ++q) {
+      const int r0 = 2 * q;
+      const uint32_t read = (uint32_t)((rs0 + (uint64_t)r0) >> 1);
+      const uint64_t off = __shfl_sync(0xffffffffu, my_off, r0);
+      const int l = __shfl_sync(0xffffffffu, my_l, r0);
+      const int n_s = l - k + 1;
+      uint8_t *codes_f = A.codes + 2 * off, *codes_r = codes_f + l;
+      uint32_t *pw_f = warp_base + (size_t)r0 * B.words_per_rs + o_pw, *pw_r = pw_f + B.words_per_rs;
+      int amb_f = 0, amb_r = 0;
+      bool noncanon = false;
+      uint32_t any_amb = 0;
+      const int n_words = (l + 15) / 16 + 1;
+      for (int base0 = 0; base0 < n_words * 16; base0 += 128) {
+        if (base0 + 128 < n_words * 16) fetch(r0, base0 + 128, nxt);
+        else if (r0 + 2 < n_here) fetch(r0 + 2, 0, nxt);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i0 = base0 + u * 32, i = i0 + (int)lane;
+          if (i0 >= n_words * 16) break;
+          const bool valid = i < l;
+          uint32_t c = 0;
+          if (valid) {
+            const uint32_t ch = cur[u];
+            const uint32_t two = ((ch >> 1) & 3u) ^ ((ch >> 2) & 1u);
+            const bool acgt = ((0x54474341u >> (8u * two)) & 0xFFu) == ch;
+            noncanon |= !(acgt || ch == 'N');
+            c = acgt ? two : 4u;
+            codes_f[i] = (uint8_t)c;
+            codes_r[l - 1 - i] = (uint8_t)(acgt ? 3u - two : 4u); // ambiguous stays ambiguous on the reverse strand
+          }
+          const uint32_t amb4 = __ballot_sync(0xffffffffu, valid && c == 4u);
+          if (amb4) { // only incoming bases count (utils.h:113): forward i >= k, reverse l - 1 - i >= k
+            const int nf = k - i0, nr = l - k - i0;
+            const uint32_t mask_f = nf <= 0 ? 0xFFFFFFFFu : nf >= 32 ? 0u : 0xFFFFFFFFu << nf;
+            const uint32_t mask_r = nr <= 0 ? 0u : nr >= 32 ? 0xFFFFFFFFu : (1u << nr) - 1u;
+            amb_f += __popc(amb4 & mask_f);
+            amb_r += __popc(amb4 & mask_r);
+            any_amb = 1;
+          }
+          uint32_t v = (valid && c < 4u) ? c << (30 - 2 * (i & 15)) : 0u;          // ambiguous hashed as A
+          v |= __shfl_xor_sync(0xffffffffu, v, 8);
+          v |= __shfl_xor_sync(0xffffffffu, v, 4);
+          v |= __shfl_xor_sync(0xffffffffu, v, 2);
+          v |= __shfl_xor_sync(0xffffffffu, v, 1);
+          if ((lane & 15u) == 0 && (i >> 4) < n_words) pw_f[i >> 4] = v;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) cur[u] = nxt[u];
+      }
+      __syncwarp();
+      for (int w = (int)lane; w < n_words; w += 32) {
+        const int s0 = l - 16 - 16 * w;            // first forward base of the window, may lie before the read
+        const int a0 = s0 >> 4, sh = 2 * (s0 & 15); // floor division: s0 = 16 * a0 + (s0 & 15)
+        const uint32_t hi = a0 >= 0 && a0 < n_words ? pw_f[a0] : 0u;
+        const uint32_t lo = a0 + 1 >= 0 && a0 + 1 < n_words ? pw_f[a0 + 1] : 0u;
+        uint32_t x = __brev(__funnelshift_l(lo, hi, sh));
+        x = ((x & 0x55555555u) << 1) | ((x >> 1) & 0x55555555u);
+        pw_r[w] = ~x;
+      }
+      if (any_amb) {
+        __syncwarp();
+        for (int i = (int)lane; i < l; i += 32)
+          if (codes_f[i] == 4) {
+            const int j = l - 1 - i;
+            atomicAnd(&pw_r[j >> 4], ~(3u << (30 - 2 * (j & 15))));
+          }
+      }
+      const bool any_noncanon = __any_sync(0xffffffffu, noncanon);
+      if (lane == 0) A.read_flags[read] = any_noncanon ? 1 : 0;
+#pragma unroll
+      for (int d = 0; d < 2; ++d) {
+        const int amb = d ? amb_r : amb_f;
+        uint32_t status = RS_OK;
+        if (n_s <= 0) status = RS_INFEASIBLE;                                              // reference: assert, filter.c:167
+        else if ((uint32_t)Q > div_small((uint32_t)n_s, B.inv_step)) status = RS_EMPTY;     // filter.c:168-172
+        else if (amb > A.e) status = RS_EMPTY;                                              // filter.c:180-182
+        else if (n_s - (step - 1) < 0 || div_small((uint32_t)(n_s - (step - 1)), B.inv_step) < (uint32_t)(Q * s)) status = RS_INFEASIBLE;
+        if ((int)lane == r0 + d) { my_status = status; my_ns = n_s; }
+      }
+    }
+  } else
   for (int r = 0; r < n_here; ++r) {
     const uint64_t rs = rs0 + (uint64_t)r;
     const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
