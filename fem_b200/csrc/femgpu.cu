@@ -20,7 +20,6 @@
 #include "k_cand_pair.cuh"
 #include "k_cand_pair32.cuh"
 #include "k_cand_small.cuh"
-#include "k_cand_small_v1.cuh"
 #include "k_index.cuh"
 #include "k_peak.cuh"
 #include "k_seed.cuh"
@@ -224,7 +223,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char *b = getenv("FEM_BLOCKING_SYNC")) c->blocking_sync = atoi(b) != 0;
   if (const char *m = getenv("FEM_CAND_MODE")) { const int v = atoi(m); if (v >= 0 && v <= 4) c->cand_mode = v; } // experiments: see "cand_mode"
-  if (const char *m = getenv("FEM_SMALL_SHAPE")) { const int v = atoi(m); if (v == 1 || v == 4 || v == 9) c->small_shape = v; } // experiments: see "small_shape"
+  if (const char *m = getenv("FEM_SMALL_SHAPE")) { const int v = atoi(m); if (v == 1 || v == 4) c->small_shape = v; } // experiments: see "small_shape"
   if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
   for (auto &s : c->slot) {
     if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -271,7 +270,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
   else if (k == "cand_mode" && value >= 0 && value <= 4) c->cand_mode = (int)value;
-  else if (k == "small_shape" && (value == 0 || value == 1 || value == 4 || value == 9)) c->small_shape = (int)value;
+  else if (k == "small_shape" && (value == 0 || value == 1 || value == 4)) c->small_shape = (int)value;
   else if (k == "pair_layout" && (value == 0 || value == 32 || value == 64)) c->pair_layout = (int)value;
   else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 32768 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;

@@ -100,7 +100,6 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     const bool narrow = (uint32_t)(pl->Q * pl->step) <= 32u && per_rs <= 0.5 * SMALL_CAP_NARROW;
     pl->small_R = c->small_shape == 4 ? 4 : c->small_shape == 1 ? ((uint32_t)(pl->Q * pl->step) <= 32u ? 1 : 4) : (narrow ? 1 : 4);
     pl->small_smem = 4 * (pl->small_R == 1 ? SmallShape<1>::bytes_per_warp() : SmallShape<4>::bytes_per_warp());
-    if (c->small_shape == 9) { pl->small_R = 9; pl->small_smem = 4 * ((cand_small_v1_smem_bytes_per_warp() + 15) & ~(size_t)15); }
     pl->small_inv_Q = pl->Q > 1 ? (uint32_t)(0x100000000ull / (uint64_t)pl->Q) + 1u : 0u;
     if (c->cand_mode == 4 || (c->cand_mode == 0 && fits && per_rs <= 128.0)) pl->first_path = 3;
     if (c->cand_mode == 3 && pl->a < 1) pl->first_path = 1;
@@ -248,7 +247,6 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.rs_list = nullptr;
     ca.n_list = 0;
     if (pl.first_path == 3 && pl.small_R == 1) k_cand_small<1><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
-    else if (pl.first_path == 3 && pl.small_R == 9) k_cand_small_v1<<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca);
     else if (pl.first_path == 3) k_cand_small<4><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
     else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
