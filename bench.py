@@ -165,7 +165,7 @@ class ClockSampler:
         sm = sorted(x[0] for x in self.samples)
         reasons = sorted(k for k, b in bits.items() if any(x[1] & b for x in self.samples))
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
-                "samples": len(sm), "power_w_max": max((x[2] for x in self.samples), default=0.0), "source": "nvml, 2 ms period"}
+                "samples": len(sm), "power_w_max": max((x[2] for x in self.samples), default=0.0), "source": "nvml polled with 2 ms pauses, from the start of the resident leg to the end of the end-to-end leg"}
 
     def _pump(self):
         for line in self.proc.stdout:
@@ -360,7 +360,6 @@ def run_ours(args):
         launches += nl.value
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
-    clocks = sampler.stop()
     work = (C.c_uint64 * 4)()
     _check(lib.femgpu_last_work(ctx, C.byref(work)))
     dev_ms = max_over_ranks(dev_ms)
@@ -383,6 +382,7 @@ def run_ours(args):
         e2e_stats, tm = hm.map_file(fq, out, w["e"], w["a"], threads=threads, batch_reads=args.e2e_batch)
         e2e_s += time.perf_counter() - e0
     barrier()
+    clocks = sampler.stop()  # sampled from the start of the resident leg to the end of the end-to-end leg
     e2e_s = max_over_ranks(e2e_s)
     sam_bytes = os.path.getsize(out)
     os.remove(out)
