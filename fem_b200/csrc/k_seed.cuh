@@ -107,24 +107,12 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
   if (status == RS_OK) {
     // ---- hashes and lookup-table gathers (two adjacent uint32 per q-gram) --------------------
     const uint32_t mask = (uint32_t)((1ull << (2 * k)) - 1);
-    for (int p0 = 0; p0 < n_s; p0 += 128) { // four q-grams per lane: eight gathers in flight before any is used
-      uint32_t b[4], e2[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int p = p0 + u * 32 + (int)lane;
-        b[u] = e2[u] = 0;
-        if (p < n_s) {
-          const uint64_t x = ((uint64_t)pw[p >> 4] << 32) | pw[(p >> 4) + 1];
-          const uint32_t h = (uint32_t)(x >> (64 - 2 * (p & 15) - 2 * k)) & mask;
-          b[u] = __ldg(A.lut + h);
-          e2[u] = __ldg(A.lut + h + 1);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int p = p0 + u * 32 + (int)lane;
-        if (p < n_s) { sm_begin[p] = b[u]; sm_freq[p] = e2[u] - b[u]; }
-      }
+    for (int p = (int)lane; p < n_s; p += 32) {
+      const uint64_t x = ((uint64_t)pw[p >> 4] << 32) | pw[(p >> 4) + 1];
+      const uint32_t h = (uint32_t)(x >> (64 - 2 * (p & 15) - 2 * k)) & mask;
+      const uint32_t b = __ldg(A.lut + h), e2 = __ldg(A.lut + h + 1);
+      sm_begin[p] = b;
+      sm_freq[p] = e2 - b;
     }
     __syncwarp();
     bool bad = false; // fewer than Q seeds found: the reference reads uninitialised memory
