@@ -203,6 +203,14 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     sm.inv_Q = (uint32_t)(0x100000000ull / (uint64_t)pl.Q) + 1u;
     sm.inv_stepQ = (uint32_t)(0x100000000ull / (uint64_t)(pl.step * pl.Q)) + 1u;
     if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
+    // L1 / shared-memory split: the kernel's gathers and byte stores live on L1 hits, so half of the 256 KB goes to
+    // L1 (six blocks of ~20 KB per SM instead of ten).  Measured on cfg2 per 1 M reads: default split (ten blocks)
+    // 2.05 ms, 80 % shared 2.12, 70 % 1.81, 50 % 1.78, 40 % / 30 % 1.88, 100 % 4.0.  FEM_SEED_CARVEOUT overrides.
+    {
+      int carve = 50;
+      if (const char *cv = getenv("FEM_SEED_CARVEOUT")) carve = atoi(cv);
+      if (carve >= 0 && carve <= 100) cudaFuncSetAttribute(k_seed_multi, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    }
     const uint64_t per_block = 4ull * (uint64_t)pl.seed_R;
     k_seed_multi<<<(unsigned)((n_rs + per_block - 1) / per_block), 128, pl.seed_smem, s.stream>>>(sm);
   } else {
