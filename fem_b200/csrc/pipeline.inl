@@ -54,7 +54,10 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   pl->seed_R = 0;
   if ((c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
     pl->seed_words_per_rs = seed_multi_words_per_rs(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step);
-    int R = 32 / pl->step;
+    // read-strands per warp: as many as fill the DP's lanes, but at most four -- smaller regions mean more warps
+    // beside the L1 half of the SM (cfg2 per 1 M reads: 8 per warp 1.78 ms, 6: 1.66, 4: 1.65, 2: 2.03)
+    int R = std::min(32 / pl->step, 4);
+    if (const char *rv = getenv("FEM_SEED_R")) { const int v = atoi(rv); if (v >= 1 && v <= 32 / pl->step) R = v; } // experiments
     size_t bytes = 16ull * ((size_t)R * pl->seed_words_per_rs + SEED_MULTI_SCRATCH);
     bool use = c->seed_dp_mode == 3 || (pl->k <= 12 && bytes <= 24 * 1024 && pl->l_max <= 128 && pl->Q <= 7);
     if (c->seed_dp_mode == 3)
