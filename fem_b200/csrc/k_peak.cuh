@@ -1,29 +1,36 @@
-// k_peak.cuh -- INT32 pipe peak microbenchmark (the roofline denominator of k_verify; the driver's
-// MEASURED_PEAKS.json only holds HBM and bf16 numbers).  Each thread runs 8 independent
-// dependency chains of one instruction kind so that issue rate, not latency, is measured.
+// k_peak.cuh -- INT32 (ALU pipe) peak microbenchmark: the roofline denominator of k_verify; the driver's
+// MEASURED_PEAKS.json only holds HBM and bf16 numbers.
+//
+// Eight values per thread, coupled in a ring: round r computes a_i <- f(a_i, a_(i+1), b) for all i, so the
+// eight instructions of a round are independent of each other (issue rate, not latency, is measured) while
+// every new value has a fresh second input.  That coupling is what keeps ptxas from folding the chain:
+// iterating f(a, b, c) with loop-invariant b and c -- the first version of this probe -- is again a
+// function of three inputs and collapsed into far fewer LOP3 / one multiply-add (readings of
+// 2.4e7 and 3.7e4 Gop/s).  The instructions are written as PTX so that the count per round is exact;
+// `cuobjdump -sass` of this kernel shows 128 LOP3 / 128 IADD3 / 128 SHF + 128 LOP3 per loop trip.
 #pragma once
 #include "common.cuh"
 
-template <int KIND> // 0: LOP3 (a ^ b & c), 1: IADD3, 2: SHF/shift + LOP3 mix as in the Myers column
+#define FEM_PEAK_ROUNDS 16 // rounds per loop trip: 16 x 8 = 128 instructions of the kind (x 2 for kind 2)
+
+template <int KIND> // 0: LOP3, 1: IADD3, 2: SHF + LOP3 as in the Myers column (two instructions per step)
 __global__ void __launch_bounds__(256) k_int_peak(uint32_t *out, int iters, uint32_t seed) {
   uint32_t a0 = seed + threadIdx.x, a1 = a0 * 3, a2 = a0 * 5, a3 = a0 * 7, a4 = a0 * 11, a5 = a0 * 13, a6 = a0 * 17, a7 = a0 * 19;
-  const uint32_t b = seed * 0x9E3779B9u + blockIdx.x, c = ~seed;
+  const uint32_t b = seed * 0x9E3779B9u + blockIdx.x;
+#define FEM_PEAK_STEP(x, y)                                                                              \
+  if (KIND == 0) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x) : "r"(y), "r"(b));               \
+  else if (KIND == 1) asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(x) : "r"(y), "r"(b)); \
+  else asm volatile("{ .reg .u32 t; shr.u32 t, %0, 1; xor.b32 %0, t, %1; }" : "+r"(x) : "r"(y));
 #pragma unroll 1
   for (int i = 0; i < iters; ++i) {
 #pragma unroll
-    for (int u = 0; u < 16; ++u) {
-      if (KIND == 0) {
-        a0 = (a0 ^ b) & (a0 | c); a1 = (a1 ^ b) & (a1 | c); a2 = (a2 ^ b) & (a2 | c); a3 = (a3 ^ b) & (a3 | c);
-        a4 = (a4 ^ b) & (a4 | c); a5 = (a5 ^ b) & (a5 | c); a6 = (a6 ^ b) & (a6 | c); a7 = (a7 ^ b) & (a7 | c);
-      } else if (KIND == 1) {
-        a0 = a0 + b + c; a1 = a1 + b + c; a2 = a2 + b + c; a3 = a3 + b + c;
-        a4 = a4 + b + c; a5 = a5 + b + c; a6 = a6 + b + c; a7 = a7 + b + c;
-      } else {
-        a0 = (a0 >> 1) ^ b; a1 = (a1 >> 1) ^ b; a2 = (a2 >> 1) ^ b; a3 = (a3 >> 1) ^ b;
-        a4 = (a4 >> 1) ^ b; a5 = (a5 >> 1) ^ b; a6 = (a6 >> 1) ^ b; a7 = (a7 >> 1) ^ b;
-      }
+    for (int u = 0; u < FEM_PEAK_ROUNDS; ++u) {
+      // the ring closes on the a0 of this round: seven instructions later, beyond the pipe's latency of four
+      FEM_PEAK_STEP(a0, a1) FEM_PEAK_STEP(a1, a2) FEM_PEAK_STEP(a2, a3) FEM_PEAK_STEP(a3, a4)
+      FEM_PEAK_STEP(a4, a5) FEM_PEAK_STEP(a5, a6) FEM_PEAK_STEP(a6, a7) FEM_PEAK_STEP(a7, a0)
     }
   }
+#undef FEM_PEAK_STEP
   const uint32_t r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
   if (r == 0x12345678u) out[0] = r; // keeps the chains alive
 }

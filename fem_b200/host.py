@@ -37,7 +37,8 @@ class StrStruct(C.Structure):
 
 class MapOptions(C.Structure):
     _fields_ = [("params", Params), ("n_threads", C.c_int32), ("batch_reads", C.c_uint32), ("skip_reads", C.c_uint64),
-                ("max_reads", C.c_uint64), ("no_header", C.c_int32)]
+                ("max_reads", C.c_uint64), ("no_header", C.c_int32), ("no_reads", C.c_int32), ("shard_index", C.c_uint32),
+                ("shard_count", C.c_uint32)]
 
 
 class MapTiming(C.Structure):
@@ -58,6 +59,8 @@ EXPORTS = {
     "femhost_reader_next": (C.c_int64, [C.c_void_p, C.c_uint32, C.POINTER(RecordsStruct)]),
     "femhost_load_all": (C.c_int, [C.c_char_p, C.POINTER(RecordsStruct)]),
     "femhost_load_all_ranges": (C.c_int, [C.c_char_p, C.c_uint64, C.POINTER(RecordsStruct)]),
+    "femhost_load_shard": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, C.POINTER(RecordsStruct)]),
+    "femhost_count_records": (C.c_int64, [C.c_char_p]),
     "femhost_index_build": (C.c_int, [C.POINTER(RecordsStruct), C.c_int, C.c_int, C.POINTER(IndexStruct)]),
     "femhost_index_build_device": (C.c_int, [C.POINTER(RecordsStruct), C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_double * 3)]),
     "femhost_index_save": (C.c_int, [C.POINTER(IndexStruct), C.c_char_p]),
@@ -160,6 +163,34 @@ def load_all_ranges(path, chunk_bytes):
     if rc != 0:
         raise FemGpuError(_err())
     return r
+
+
+ENOTFASTQ4 = -5  # femhost.h FEMHOST_ENOTFASTQ4
+
+
+class NotFastq4(FemGpuError):
+    """byte-range shards do not apply to this input: every rank falls back to read-count shards"""
+
+
+def load_shard(path, shard_index, shard_count):
+    """-> Records of byte-range shard shard_index of shard_count (the cut HostMapper.map_file(shard=...) makes),
+    or None when the file is not plain four-line FASTQ."""
+    r = Records()
+    rc = r.lib.femhost_load_shard(os.fsencode(path), shard_index, shard_count, C.byref(r.c))
+    if rc == 1:
+        r.close()
+        return None
+    if rc != 0:
+        raise FemGpuError(_err())
+    return r
+
+
+def count_records(path):
+    """records the readers deliver for any accepted input (FASTA/FASTQ, multi-line, gzip)"""
+    n = load_host_library().femhost_count_records(os.fsencode(path))
+    if n < 0:
+        raise FemGpuError(_err())
+    return int(n)
 
 
 def read_batches(path, batch):
@@ -276,11 +307,16 @@ class HostMapper:
             raise FemGpuError(_err())
 
     def map_file(self, reads_path, sam_path, e, a=1, threads=1, k=0, step=0, batch_reads=0, skip_reads=0, max_reads=0,
-                 no_header=False):
-        opt = MapOptions(Params(k, step, e, a), threads, batch_reads, skip_reads, max_reads, int(no_header))
+                 no_header=False, no_reads=False, shard=None):
+        """shard=(index, count): byte-range shard of a plain four-line FASTQ file (raises NotFastq4 otherwise);
+        skip_reads / max_reads / no_reads: read-count shard of any input."""
+        si, sc = shard if shard else (0, 0)
+        opt = MapOptions(Params(k, step, e, a), threads, batch_reads, skip_reads, max_reads, int(no_header), int(no_reads), si, sc)
         st, tm = Stats(), MapTiming()
         rc = self.lib.femhost_map_file(self.h, C.byref(opt), os.fsencode(reads_path),
                                        os.fsencode(sam_path) if sam_path else None, C.byref(st), C.byref(tm))
+        if rc == ENOTFASTQ4:
+            raise NotFastq4(_err())
         if rc != 0:
             raise FemGpuError(_err())
         return st.as_tuple(), tm.as_dict()

@@ -273,6 +273,7 @@ typedef struct {
   /* parallel reader (plain four-line FASTQ): the file is cut into byte ranges, batch = range */
   int fd;
   uint64_t file_size, chunk_bytes, n_chunks, next_chunk;
+  uint64_t range_lo, range_hi; /* this run's byte range of the file (the whole file unless sharded) */
   int readers_left;
   int restart_sequential;   /* some range did not parse as four-line FASTQ: run again with the kseq reader */
   int failed;
@@ -294,7 +295,7 @@ static void run_fail(run_state *r, const char *msg) {
 static void *reader_main(void *arg) {
   run_state *r = (run_state *)arg;
   const uint32_t per_batch = r->opt->batch_reads ? r->opt->batch_reads : DEFAULT_BATCH_READS;
-  uint64_t to_skip = r->opt->skip_reads, left = r->opt->max_reads ? r->opt->max_reads : UINT64_MAX, seq = 0;
+  uint64_t to_skip = r->opt->skip_reads, left = r->opt->no_reads ? 0 : r->opt->max_reads ? r->opt->max_reads : UINT64_MAX, seq = 0;
   double busy = 0;
   batch *b = NULL;
   while (left && !r->failed) {
@@ -338,7 +339,7 @@ static void *reader_main(void *arg) {
  * only start then) */
 static uint64_t par_range_start(const run_state *r, uint64_t i) {
   static const uint64_t eighths[4] = {0, 1, 2, 4};
-  return i < 4 ? r->chunk_bytes * eighths[i] / 8 : (i - 3) * r->chunk_bytes;
+  return r->range_lo + (i < 4 ? r->chunk_bytes * eighths[i] / 8 : (i - 3) * r->chunk_bytes);
 }
 
 static int64_t par_sync(run_state *r, uint64_t a, unsigned char *win, size_t win_cap) {
@@ -371,7 +372,7 @@ static void *par_reader_main(void *arg) {
     if (i == UINT64_MAX) { fifo_push(&r->q_free, b); break; }
     const double t0 = femhost_now();
     const int64_t lo = par_sync(r, par_range_start(r, i), win, win_cap);
-    const int64_t hi = i + 1 == r->n_chunks ? (int64_t)r->file_size : par_sync(r, par_range_start(r, i + 1), win, win_cap);
+    const int64_t hi = par_sync(r, i + 1 == r->n_chunks ? r->range_hi : par_range_start(r, i + 1), win, win_cap);
     int rc = lo < 0 || hi < lo ? 1 : 0;
     if (!rc) {
       const size_t n = (size_t)(hi - lo);
@@ -632,7 +633,7 @@ static void *writer_main(void *arg) {
     for (uint32_t c = 0; c < b->n_chunks; ++c) {
       const size_t len = b->items[c].ext ? b->items[c].ext_len : b->text[c].l;
       r->tm.sam_bytes += len;
-      if (r->out_fd < 0 || !len) continue;
+      if (r->out_fd < 0 || !len || r->failed || r->restart_sequential) continue;
       if (!r->out_seekable) { /* pipe: in order, from this thread */
         if (write_all(r->out_fd, b->items[c].ext ? b->items[c].ext : b->text[c].s, len, 0, 0)) run_fail(r, "short write to the SAM file");
         continue;
@@ -763,8 +764,15 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
     const uint64_t per_batch = opt->batch_reads ? opt->batch_reads : DEFAULT_BATCH_READS;
     r.chunk_bytes = per_batch * 224; /* about per_batch reads of 100 bp; only the batch granularity depends on it */
     if (r.chunk_bytes < 4096) r.chunk_bytes = 4096;
+    /* one process per GPU: shard i of n takes the records that start in [sync(size*i/n), sync(size*(i+1)/n)) */
+    r.range_lo = 0;
+    r.range_hi = r.file_size;
+    if (opt->shard_count > 1) {
+      r.range_lo = (uint64_t)((__uint128_t)r.file_size * opt->shard_index / opt->shard_count);
+      r.range_hi = (uint64_t)((__uint128_t)r.file_size * (opt->shard_index + 1) / opt->shard_count);
+    }
     r.n_chunks = 0;
-    while (par_range_start(&r, r.n_chunks) < r.file_size) ++r.n_chunks;
+    while (par_range_start(&r, r.n_chunks) < r.range_hi) ++r.n_chunks;
     r.readers_left = par_readers(opt->n_threads);
   } else {
     r.rd = femhost_reader_open(reads_path);
@@ -895,22 +903,53 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
 }
 
 /* ---- src/FEM_map.c:146-219 ------------------------------------------------------------------------ */
+/* a path that exists and is not a regular file (FIFO, /dev/stdout, a socket): bytes written to it
+ * cannot be taken back, so the run must not start over after it has emitted any */
+static int output_is_stream(const char *sam_path) {
+  struct stat st;
+  return sam_path && stat(sam_path, &st) == 0 && !S_ISREG(st.st_mode);
+}
+
 int femhost_map_file(femhost_mapper *m, const femhost_map_options *opt, const char *reads_path, const char *sam_path,
                      femgpu_stats *stats, femhost_map_timing *timing) {
   if (!m || !opt || !reads_path) return femhost_set_error(-1, "map: null argument");
   if (opt->params.e < 0 || opt->params.e > 7) return femhost_set_error(-1, "Wrong error threshold.");         /* src/FEM_map.c:30 */
   if (opt->n_threads <= 0 || opt->n_threads > 1024) return femhost_set_error(-1, "Wrong number of threads."); /* :34 */
   if (opt->params.a < 0 || opt->params.a > 2) return femhost_set_error(-1, "Wrong number of additional q-grams."); /* :38 */
+  const int sharded = opt->shard_count > 1;
+  if (sharded && opt->shard_index >= opt->shard_count) return femhost_set_error(-1, "map: shard %u of %u", opt->shard_index, opt->shard_count);
+  if (sharded && (opt->skip_reads || opt->max_reads || opt->no_reads))
+    return femhost_set_error(-1, "map: byte-range shards and read-count shards exclude each other");
   uint64_t size = 0;
   const char *force = getenv("FEM_READER"); /* "kseq": always the sequential reader */
-  int parallel = opt->skip_reads == 0 && opt->max_reads == 0 && !(force && strcmp(force, "kseq") == 0) &&
-                 parallel_readable(reads_path, &size);
+  /* The parallel reader starts over with the sequential one when some range is not four-line FASTQ; that
+   * is only possible while nothing irrevocable has been written, i.e. with a regular output file. */
+  int parallel = opt->skip_reads == 0 && opt->max_reads == 0 && !opt->no_reads && !(force && strcmp(force, "kseq") == 0) &&
+                 !output_is_stream(sam_path) && parallel_readable(reads_path, &size);
+  if (sharded && !parallel)
+    return femhost_set_error(FEMHOST_ENOTFASTQ4, "map: byte-range shards need a plain four-line FASTQ file and a regular output file");
   int restart = 0;
   const double t0 = femhost_now();
   int rc = map_file_run(m, opt, reads_path, sam_path, parallel, stats, timing, &restart);
+  if (rc == 0 && restart && sharded) /* the other shards cannot know: the caller repeats the run with read-count shards */
+    return femhost_set_error(FEMHOST_ENOTFASTQ4, "map: %s is not plain four-line FASTQ, byte-range shards do not apply", reads_path);
   if (rc == 0 && restart) { /* not plain four-line FASTQ after all: once more, sequentially */
     rc = map_file_run(m, opt, reads_path, sam_path, 0, stats, timing, &restart);
     if (timing) timing->wall = femhost_now() - t0;
   }
   return rc;
+}
+
+/* records of a sequence file as femhost_map_file's readers see them (zero-length records skipped,
+ * FASTA, multi-line and gzip input included): what read-count shards are cut from */
+int64_t femhost_count_records(const char *path) {
+  femhost_reader *rd = femhost_reader_open(path);
+  if (!rd) return -1;
+  femhost_records tmp;
+  femhost_records_init(&tmp, 0);
+  int64_t total = 0, n;
+  while ((n = femhost_reader_next(rd, 1u << 16, &tmp)) > 0) total += n;
+  femhost_records_free(&tmp);
+  femhost_reader_close(rd);
+  return n < 0 ? n : total;
 }

@@ -402,3 +402,45 @@ int femhost_load_all_ranges(const char *path, uint64_t chunk_bytes, femhost_reco
   free(buf);
   return rc;
 }
+
+/* One byte-range shard of a plain four-line FASTQ file: records that start in
+ * [sync(size*i/n), sync((i+1)*size/n)), exactly the cut femhost_map_file makes for
+ * femhost_map_options.shard_index / shard_count, so the shards concatenate to the file. */
+int femhost_load_shard(const char *path, uint32_t shard_index, uint32_t shard_count, femhost_records *out) {
+  if (shard_count == 0 || shard_index >= shard_count) return femhost_set_error(-1, "load: shard %u of %u", shard_index, shard_count);
+  FILE *f = fopen(path, "rb");
+  if (!f) return femhost_set_error(-1, "Cannot find sequence file!");
+  fseeko(f, 0, SEEK_END);
+  const uint64_t size = (uint64_t)ftello(f);
+  out->n_records = 0;
+  out->n_bases = 0;
+  int rc = femhost_records_reserve(out, 1, 16, 16) ? -3 : 0;
+  unsigned char head = 0;
+  fseeko(f, 0, SEEK_SET);
+  if (!rc && (size < 4 || fread(&head, 1, 1, f) != 1 || head != '@')) rc = 1;
+  const size_t win = 1 << 18;
+  unsigned char *w = (unsigned char *)malloc(win), *buf = NULL;
+  uint64_t lim[2] = {0, 0};
+  for (int j = 0; j < 2 && !rc; ++j) {
+    const uint64_t at = (uint64_t)((__uint128_t)size * (shard_index + (uint32_t)j) / shard_count);
+    if (at == 0) lim[j] = 0;
+    else if (at >= size) lim[j] = size;
+    else {
+      const size_t n = at + win > size ? (size_t)(size - at) : win;
+      if (fseeko(f, (off_t)at, SEEK_SET) != 0 || fread(w, 1, n, f) != n) { rc = femhost_set_error(-3, "cannot read %s", path); break; }
+      const long o = femhost_fastq4_sync(w, n, 0, at + n == size);
+      if (o < 0) rc = 1;
+      else lim[j] = at + (uint64_t)o;
+    }
+  }
+  if (!rc && lim[1] > lim[0]) {
+    const size_t n = (size_t)(lim[1] - lim[0]);
+    buf = (unsigned char *)malloc(n + 1);
+    if (!buf || fseeko(f, (off_t)lim[0], SEEK_SET) != 0 || fread(buf, 1, n, f) != n) rc = femhost_set_error(-3, "cannot read %s", path);
+    else rc = femhost_parse_fastq4(buf, buf + n, out);
+  }
+  free(buf);
+  free(w);
+  fclose(f);
+  return rc;
+}

@@ -63,6 +63,12 @@ int femhost_load_all(const char *path, femhost_records *out);
  * reader does: independent byte ranges of chunk_bytes that resynchronise on record starts.
  * Returns 1 (and callers fall back to femhost_load_all) when the file is not of that shape. */
 int femhost_load_all_ranges(const char *path, uint64_t chunk_bytes, femhost_records *out);
+/* The records femhost_map_file maps for byte-range shard shard_index of shard_count (see
+ * femhost_map_options); returns 1 when the file is not plain four-line FASTQ. */
+int femhost_load_shard(const char *path, uint32_t shard_index, uint32_t shard_count, femhost_records *out);
+/* Number of records the readers deliver for a file of any accepted format (FASTA/FASTQ, multi-line,
+ * gzip; zero-length records are skipped as in src/sequence_batch.c:50-52), or a negative error. */
+int64_t femhost_count_records(const char *path);
 
 /* ---- index ------------------------------------------------------------------------------------ */
 /* src/index.h:7-14 */
@@ -125,7 +131,15 @@ typedef struct {
   uint64_t skip_reads;    /* one process per GPU: this process maps reads                      */
   uint64_t max_reads;     /*   [skip_reads, skip_reads + max_reads) of the file (0 = to the end)*/
   int32_t no_header;      /* and only the first shard prints the @SQ lines                     */
+  int32_t no_reads;       /* this process maps nothing (more shards than reads); max_reads = 0 means "to the end" */
+  uint32_t shard_index;   /* shard_count > 1: this process maps the records that START in byte range            */
+  uint32_t shard_count;   /*   [size*index/count, size*(index+1)/count) of a plain four-line FASTQ file -- no    */
+                          /*   counting pass, no skipped reads; other inputs return FEMHOST_ENOTFASTQ4          */
 } femhost_map_options;
+/* femhost_map_file with shard_count > 1 on input that is not plain four-line FASTQ (FASTA, gzip, CRLF,
+ * multi-line records): every rank must then fall back to read-count shards (skip_reads / max_reads
+ * from femhost_count_records), see fem_b200/shard.py */
+#define FEMHOST_ENOTFASTQ4 (-5)
 
 /* per-phase host seconds of the last run (summed over threads where parallel) */
 typedef struct {

@@ -117,6 +117,98 @@ def test_read_shards_concatenate_to_the_whole(big):
     assert tuple(total) == big["counters"]
 
 
+def test_byte_range_shards_concatenate_to_the_whole(big):
+    """One process per GPU on a plain four-line FASTQ file: rank r maps the records that start in byte range r of n
+    (femhost_map_options.shard_index / shard_count) -- no counting pass, nothing parsed twice.  The parts in rank order
+    are the single-process file; input of another shape is refused with FEMHOST_ENOTFASTQ4, never mapped in part."""
+    from fem_b200 import host
+    m = host.HostMapper(big["fa"], big["idx"], 1)
+    for n in (2, 3, 8):
+        parts, total = [], [0] * 5
+        for r in range(n):
+            out = str(big["d"] / ("bshard%d.sam" % r))
+            st, _ = m.map_file(big["fq"], out, big["e"], big["a"], threads=3, batch_reads=1201, no_header=r > 0, shard=(r, n))
+            assert st[0] == len(host.load_shard(big["fq"], r, n))
+            total = [x + y for x, y in zip(total, st[:5])]
+            with open(out, "rb") as f:
+                parts.append(f.read())
+        assert b"".join(parts) == big["want"], n
+        assert tuple(total) == big["counters"]
+    zipped = str(big["d"] / "shard_reads.fq.gz")
+    with open(big["fq"], "rb") as f, gzip.open(zipped, "wb", compresslevel=1) as g:
+        g.write(f.read())
+    with pytest.raises(host.NotFastq4):
+        m.map_file(zipped, str(big["d"] / "never.sam"), big["e"], big["a"], threads=2, shard=(0, 2))
+    # the read-count fall-back every rank then takes: slices cut with the real parser, explicit "no reads" for an empty slice
+    n_reads = host.count_records(zipped)
+    assert n_reads == big["n_reads"]
+    parts = []
+    for r, (skip, count) in enumerate([(0, n_reads // 2), (n_reads // 2, n_reads - n_reads // 2), (n_reads, 0)]):
+        out = str(big["d"] / ("cshard%d.sam" % r))
+        st, _ = m.map_file(zipped, out, big["e"], big["a"], threads=3, skip_reads=skip, max_reads=count, no_header=r > 0, no_reads=count == 0)
+        assert st[0] == count
+        with open(out, "rb") as f:
+            parts.append(f.read())
+    assert b"".join(parts) == big["want"] and parts[2] == b""
+    m.close()
+
+
+def test_stream_output_is_written_once(big):
+    """with a FIFO (or /dev/stdout) as the output the parallel reader's restart would send the header and
+    the first batches twice; a stream output therefore takes the sequential reader.  CRLF records and a trailing
+    blank line are the inputs that trigger the restart on a regular file."""
+    import threading
+    from fem_b200.host import FEM_BINARY
+    d = big["d"]
+    crlf = str(d / "crlf.fq")
+    with open(big["fq"], "rb") as f, open(crlf, "wb") as g:
+        g.write(f.read().replace(b"\n", b"\r\n") + b"\r\n")
+    to_file = str(d / "crlf_file.sam")
+    run_fem_map(big["fa"], big["idx"], crlf, to_file, big["e"], big["a"], threads=4, extra=("--batch", "800"))
+    with open(to_file, "rb") as f:
+        want = f.read()
+    assert want.count(b"\n") == big["want"].count(b"\n") and want.startswith(b"@SQ")
+    for src in (crlf, big["fq"]):
+        fifo = str(d / "out.fifo")
+        if os.path.exists(fifo):
+            os.remove(fifo)
+        os.mkfifo(fifo)
+        got = []
+        t = threading.Thread(target=lambda: got.append(open(fifo, "rb").read()))
+        t.start()
+        p = subprocess.run([FEM_BINARY, "map", "-e", str(big["e"]), "-a", str(big["a"]), "-t", "4", "--ref", big["fa"], "--index", big["idx"],
+                            "--read1", src, "-o", fifo, "--batch", "800"], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        t.join(timeout=120)
+        assert p.returncode == 0, p.stderr[-1000:]
+        assert got and got[0] == (want if src == crlf else big["want"])
+
+
+def test_cli_gpus2_matches_single(big):
+    """The product's multi-GPU form: ONE process, N GPUs, one input, one ordered output (`FEM map --gpus 2`; replaces
+    src/map.c:54 + src/output_queue.c:46-58).  Byte-identical to the single-GPU file with the index cloned device to
+    device (default) and loaded per device (FEM_CLONE_RESIDENT=0); femgpu_clone_resident across two devices."""
+    from fem_b200.api import load_library
+    if load_library().femgpu_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from fem_b200.host import FEM_BINARY, HostMapper
+    for clone in ("1", "0"):
+        sam = str(big["d"] / ("gpus2_%s.sam" % clone))
+        p = subprocess.run([FEM_BINARY, "map", "-e", str(big["e"]), "-a", str(big["a"]), "-t", "6", "--ref", big["fa"], "--index", big["idx"],
+                            "--read1", big["fq"], "-o", sam, "--gpus", "2", "--batch", "700"], stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                           env={**os.environ, "FEM_CLONE_RESIDENT": clone}, text=True)
+        assert p.returncode == 0, p.stderr[-2000:]
+        assert "onto 2 GPU(s)" in p.stderr
+        with open(sam, "rb") as f:
+            assert f.read() == big["want"], clone
+    m = HostMapper(big["fa"], big["idx"], 2, [1, 0])  # device order is the caller's
+    out = str(big["d"] / "gpus2_api.sam")
+    st, tm = m.map_file(big["fq"], out, big["e"], big["a"], threads=4, batch_reads=500)
+    m.close()
+    assert st[:5] == big["counters"] and tm["n_batches"] >= big["n_reads"] // 500
+    with open(out, "rb") as f:
+        assert f.read() == big["want"]
+
+
 def test_reader_paths_agree(big):
     """parallel byte-range reader (default on plain four-line FASTQ), forced sequential reader, and
     the automatic fall-back for multi-line / gzip input all give the same SAM file."""

@@ -221,6 +221,39 @@ def test_parallel_reader_ranges_equal_sequential(tmp_path):
         with open(q, "wb") as f:
             f.write(bad)
         assert host.load_all_ranges(q, 16) is None
+        assert host.load_shard(q, 1, 3) is None or bad.startswith(b"@a\nAC\nGT")  # the cut itself may land on clean lines
+    # byte-range shards (femhost_map_options.shard_index / shard_count): a partition of the file in order
+    for count in (1, 2, 3, 8, 64, 5000):
+        got = []
+        for i in range(count):
+            part = host.load_shard(p, i, count)
+            assert part is not None
+            got += part.as_list()
+        assert got == want, count
+
+
+def test_count_records_uses_the_real_parser(tmp_path):
+    """ADVICE r1: `newlines // 4` miscounts FASTA, gzip, multi-line records and a missing final newline."""
+    import gzip
+    from fem_b200 import host
+    cases = {
+        "plain.fq": (b"@a\nACGT\n+\nIIII\n@b\nAC\n+\nII\n", 2),
+        "nofinal.fq": (b"@a\nACGT\n+\nIIII\n@b\nAC\n+\nII", 2),
+        "multi.fq": (b"@a\nAC\nGT\n+\nII\nII\n@b\nAC\n+\nII\n", 2),
+        "reads.fa": (b">a\nACGT\n>b\nAC\nGT\n>c\nA\n", 3),
+        "empty_record.fa": (b">a\nACGT\n>b\n>c\nA\n", 2),  # src/sequence_batch.c:50-52: zero-length records are skipped
+        "crlf.fq": (b"@a\r\nAC\r\n+\r\nII\r\n" * 5, 5),
+        "none.fq": (b"", 0),
+    }
+    for name, (data, n) in cases.items():
+        q = str(tmp_path / name)
+        with open(q, "wb") as f:
+            f.write(data)
+        assert host.count_records(q) == n, name
+        assert len(host.load_all(q)) == n, name
+        with gzip.open(q + ".gz", "wb") as f:
+            f.write(data)
+        assert host.count_records(q + ".gz") == n, name + ".gz"
 
 
 @pytest.mark.parametrize("n", [1, 2, 40, 64, 65, 300, 70_000])
