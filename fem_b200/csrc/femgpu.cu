@@ -19,6 +19,7 @@
 #include "k_cand_hash.cuh"
 #include "k_cand_pair.cuh"
 #include "k_cand_pair32.cuh"
+#include "k_cand_reg.cuh"
 #include "k_cand_small.cuh"
 #include "k_index.cuh"
 #include "k_peak.cuh"
@@ -108,6 +109,7 @@ struct Counters {
   unsigned long long sam_flagged; // reads k_sam left to the host
   unsigned long long sam_big;     // reads with 65..SAM_BIG_MAX mappings (k_sam_big_*)
   uint32_t overflow_count;
+  uint32_t overflow_count2; // second list: what k_cand_pair (list mode) hands on after k_cand_reg
   int error_flag;
 };
 
@@ -120,7 +122,7 @@ struct Slot {
   DBuf bases, read_off, codes, rs_status, rs_before, rs_max_f, rs_sum_f;
   DBuf seed_begin, seed_freq, seed_start;
   DBuf rs_cand_first, rs_cand_count, rs_map_count, rs_map_first, block_sums;
-  DBuf cand, cand_rs, result, maps, overflow_list, counters;
+  DBuf cand, cand_rs, result, maps, overflow_list, overflow_list2, counters;
   DBuf read_flags, map_rs, aln;
   DBuf big_list, big_off, big_S, big_A, scratch, hash_list;
   DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
@@ -187,7 +189,9 @@ struct femgpu_ctx {
   int l2_persist_lut = 1;
   int small_shape = 0;  // k_cand_small: 0 automatic, 1 one seed per lane (step x Q <= 32), 4 up to 128 seeds
   int cand_mode = 0;    // 0: pair path (a >= 1) or hash path (a = 0) first, then sort path, then global scratch;
-                        // 1: sort path only; 2: hash path first; 3: pair path first (a >= 1); 4: small path first
+                        // 1: sort path only; 2: hash path first; 3: pair path first (a >= 1); 4: small path first;
+                        // 5: register form of the pair path first (k_cand_reg) whatever the index density;
+                        // 6: pair path first, never its register form
   uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
@@ -222,7 +226,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char *b = getenv("FEM_BLOCKING_SYNC")) c->blocking_sync = atoi(b) != 0;
-  if (const char *m = getenv("FEM_CAND_MODE")) { const int v = atoi(m); if (v >= 0 && v <= 4) c->cand_mode = v; } // experiments: see "cand_mode"
+  if (const char *m = getenv("FEM_CAND_MODE")) { const int v = atoi(m); if (v >= 0 && v <= 6) c->cand_mode = v; } // experiments: see "cand_mode"
   if (const char *m = getenv("FEM_SMALL_SHAPE")) { const int v = atoi(m); if (v == 1 || v == 4) c->small_shape = v; } // experiments: see "small_shape"
   if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
   for (auto &s : c->slot) {
@@ -240,7 +244,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
 static void slot_release(Slot &s) {
   DBuf *d[] = {&s.bases, &s.read_off, &s.codes, &s.rs_status, &s.rs_before, &s.rs_max_f, &s.rs_sum_f, &s.seed_begin,
                &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
-               &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.counters, &s.big_list,
+               &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.overflow_list2, &s.counters, &s.big_list,
                &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first,
                &s.names, &s.name_off, &s.quals, &s.has_qual, &s.sam_bytes, &s.sam_host, &s.sam_off, &s.sam_blocks, &s.sam_text,
                &s.sam_big_list, &s.sam_big_ord, &s.sam_big_rec_off};
@@ -269,7 +273,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "sort_capacity" && value >= 32 && value <= 8192 && (value & (value - 1)) == 0) c->sort_capacity = (uint32_t)value;
   else if (k == "acc_capacity" && value >= 1 && value <= 8192) c->acc_capacity = (uint32_t)value;
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
-  else if (k == "cand_mode" && value >= 0 && value <= 4) c->cand_mode = (int)value;
+  else if (k == "cand_mode" && value >= 0 && value <= 6) c->cand_mode = (int)value;
   else if (k == "small_shape" && (value == 0 || value == 1 || value == 4)) c->small_shape = (int)value;
   else if (k == "pair_layout" && (value == 0 || value == 32 || value == 64)) c->pair_layout = (int)value;
   else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 32768 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;

@@ -41,9 +41,11 @@ struct CandArgs {
   int *error_flag;                 // 1: arena full
   // fast-path shared-memory plan (elements per warp)
   uint32_t S, Acap;
-  // list mode of k_cand: the read-strands the hash path (k_cand_hash) handed on
+  // list mode of k_cand / k_cand_pair: the read-strands an earlier path handed on
   const uint32_t *rs_list;
   uint32_t n_list;
+  const uint32_t *n_list_dev;      // k_cand_pair: the list's length where it stands on the device (nullptr: n_list);
+  uint32_t list_first;             //   the launch covers entries [list_first, min(n_list, *n_list_dev))
   // big path
   const uint32_t *big_list;        // read-strand ids
   const uint64_t *big_off;         // scratch offset (elements) per entry

@@ -44,8 +44,12 @@ __device__ __forceinline__ uint32_t pair_bucket(uint64_t v, uint32_t mask) {
 __global__ void __launch_bounds__(128) k_cand_pair(CandArgs A, uint32_t M, uint32_t VC) {
   extern __shared__ uint64_t smem_pair[];
   const uint32_t lane = lane_id(), wib = threadIdx.x >> 5;
-  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-  if (rs >= A.n_rs) return;
+  uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+  if (A.rs_list) { // list mode: the read-strands k_cand_reg handed on; the list's length may still stand on the device
+    rs += A.list_first;
+    if (rs >= A.n_list || (A.n_list_dev && rs >= *A.n_list_dev)) return;
+    rs = A.rs_list[rs];
+  } else if (rs >= A.n_rs) return;
   if (A.rs_status[rs] != RS_OK) {
     if (lane == 0) { A.rs_cand_first[rs] = 0; A.rs_cand_count[rs] = 0; }
     return;

@@ -1,5 +1,8 @@
 // pipeline.inl -- the per-batch device pipeline (included by femgpu.cu)
 
+#define REG_UA 16          // load slots per lane of k_cand_reg (runs of up to 16 * LPR - 3 entries)
+#define REG_CHAIN 16384ull // warps of the k_cand_pair launch chained behind k_cand_reg on the device
+
 struct Plan { // derived from params + the batch
   int k, step, e, a, Q, s;
   int l_max, n_words_max, ns_max, w_max, lane_dp;
@@ -10,8 +13,9 @@ struct Plan { // derived from params + the batch
   uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
   size_t hash_smem;
   uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
-  size_t pair_smem, pair32_smem;
+  size_t pair_smem, pair32_smem, reg_smem;
   bool pair32;
+  bool pair_reg; // k_cand_reg first (shape instantiated for this Q and runs expected to fit its slots)
   int first_path; // 0 sort, 1 hash, 2 pair, 3 small
   size_t small_smem;
   int small_R;          // k_cand_small shape: 1 (one seed per lane) or 4
@@ -96,6 +100,19 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
   {
+    // register form of the pair path: its slots hold runs of up to UA * LPR - 3 entries (and a last run of 96); a
+    // run that does not fit sends its read-strand to k_cand_pair at ~2.5 x the cost, so it is chosen while the runs
+    // of a uniform index stay below that by 3.3 standard deviations (~2 % of the read-strands of a batch hand on)
+    const double mean = (double)c->n_occ / (double)(1ull << (2 * pl->k));
+    const int lpr = pl->Q > 1 ? 32 / (pl->Q - 1) : 32;
+    const bool shape = pl->Q == 5 || pl->Q == 7 || pl->Q == 9;
+    const bool fits = mean + 3.3 * std::sqrt(mean) + 1.0 <= (double)(REG_UA * lpr - 3) && mean + 6.0 * std::sqrt(mean) <= 32.0 * PREG_UB;
+    pl->reg_smem = 4 * cand_reg_smem_bytes_per_warp(pl->pair_M);
+    pl->pair_reg = pl->a >= 1 && shape && !pl->pair32 && c->cand_mode != 6 && (c->cand_mode == 5 || ((c->cand_mode == 0 || c->cand_mode == 3) && fits)) &&
+                   pl->reg_smem <= c->smem_optin;
+    if (c->cand_mode == 5 || c->cand_mode == 6) pl->first_path = pl->a >= 1 ? 2 : 1;
+  }
+  {
     // sparse index: all groups of a read-strand at once when their lists are expected to hold <= 128 entries
     // (expectation over random q-grams; the DP picks the rarest, cfg5: 104 expected, 47 found)
     const double per_rs = (double)c->n_occ / (double)(1ull << (2 * pl->k)) * pl->Q * pl->step;
@@ -130,6 +147,7 @@ static int slot_reserve(femgpu_ctx *c, Slot &s, const Plan &pl, uint32_t n_reads
   TRY(s.rs_map_first.reserve((n_rs + 1) * 8));
   TRY(s.block_sums.reserve((n_rs / SCAN_BLOCK + 2) * 8));
   TRY(s.overflow_list.reserve(n_rs * 4 + 16));
+  TRY(s.overflow_list2.reserve(n_rs * 4 + 16));
   TRY(s.counters.reserve(sizeof(Counters)));
   TRY(s.h_counters.reserve(sizeof(Counters)));
   TRY(s.h_first.reserve((n_reads + 1ull) * 8));
@@ -248,6 +266,13 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
   if (pl.pair32_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair32_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
+  if (pl.pair_reg && pl.reg_smem > 48 * 1024) {
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<7, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<5, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+  }
 
   Counters hc;
   for (int attempt = 0;; ++attempt) {
@@ -257,9 +282,31 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ca.cand_cap = s.cand_cap;
     ca.rs_list = nullptr;
     ca.n_list = 0;
+    const bool reg_first = pl.first_path == 2 && pl.pair_reg;
     if (pl.first_path == 3 && pl.small_R == 1) k_cand_small<1><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
     else if (pl.first_path == 3) k_cand_small<4><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
     else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
+    else if (reg_first) {
+      const unsigned grid = (unsigned)((n_rs + 3) / 4);
+      static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 0; // experiments: preg_mark
+      if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 1><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 2><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 9) k_cand_reg<9, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 7) k_cand_reg<7, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else k_cand_reg<5, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      ++s.n_launches;
+      // what it hands on goes to k_cand_pair without a trip to the host: the list's length is read on the device;
+      // REG_CHAIN warps are launched, a longer list (seen below) gets a second launch for its tail
+      CandArgs c2 = ca;
+      c2.rs_list = s.overflow_list.as<uint32_t>();
+      c2.n_list = 0xFFFFFFFFu;
+      c2.n_list_dev = &dc->overflow_count;
+      c2.list_first = 0;
+      c2.overflow_list = s.overflow_list2.as<uint32_t>();
+      c2.overflow_count = &dc->overflow_count2;
+      const uint32_t chain = (uint32_t)std::min<uint64_t>(n_rs, REG_CHAIN);
+      k_cand_pair<<<(chain + 3) / 4, 128, pl.pair_smem, s.stream>>>(c2, pl.pair_M, pl.pair_VC);
+    }
     else if (pl.first_path == 2) k_cand_pair<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC);
     else if (pl.first_path == 1) k_cand_hash<<<(unsigned)((n_rs + 3) / 4), 128, pl.hash_smem, s.stream>>>(ca, pl.hash_T, pl.hash_shift);
     else k_cand<<<(unsigned)((n_rs + 3) / 4), 128, pl.cand_smem, s.stream>>>(ca);
@@ -267,12 +314,30 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     CU(cudaGetLastError());
     TRY(read_counters(s, &hc));
     bool arena_full = hc.error_flag == 1;
-    if (pl.first_path != 0 && !arena_full && hc.overflow_count) {
-      // ---- sort path for the read-strands the hash path handed on ----------------------------------
-      const uint32_t n1 = hc.overflow_count;
+    uint32_t n1 = hc.overflow_count;                         // read-strands handed on by the first path ...
+    const uint32_t *list1 = s.overflow_list.as<uint32_t>();
+    if (reg_first) {
+      if (!arena_full && hc.overflow_count > REG_CHAIN) { // the tail of a list longer than the chained launch covered
+        CandArgs c2 = ca;
+        c2.rs_list = s.overflow_list.as<uint32_t>();
+        c2.n_list = hc.overflow_count;
+        c2.list_first = (uint32_t)REG_CHAIN;
+        c2.overflow_list = s.overflow_list2.as<uint32_t>();
+        c2.overflow_count = &dc->overflow_count2;
+        k_cand_pair<<<(hc.overflow_count - (uint32_t)REG_CHAIN + 3) / 4, 128, pl.pair_smem, s.stream>>>(c2, pl.pair_M, pl.pair_VC);
+        ++s.n_launches;
+        CU(cudaGetLastError());
+        TRY(read_counters(s, &hc));
+        arena_full = hc.error_flag == 1;
+      }
+      n1 = hc.overflow_count2;                               // ... here: by k_cand_pair after k_cand_reg
+      list1 = s.overflow_list2.as<uint32_t>();
+    }
+    if (pl.first_path != 0 && !arena_full && n1) {
+      // ---- sort path for the read-strands the first path handed on ----------------------------------
       TRY(s.hash_list.reserve((size_t)n1 * 4));
-      CU(cudaMemcpyAsync(s.hash_list.p, s.overflow_list.p, (size_t)n1 * 4, cudaMemcpyDeviceToDevice, s.stream));
-      CU(cudaMemsetAsync(&dc->overflow_count, 0, sizeof(uint32_t), s.stream));
+      CU(cudaMemcpyAsync(s.hash_list.p, list1, (size_t)n1 * 4, cudaMemcpyDeviceToDevice, s.stream));
+      CU(cudaMemsetAsync(&dc->overflow_count, 0, 2 * sizeof(uint32_t), s.stream)); // both lists' counters (adjacent)
       ca.rs_list = s.hash_list.as<uint32_t>();
       ca.n_list = n1;
       k_cand<<<(n1 + 3) / 4, 128, pl.cand_smem, s.stream>>>(ca);
@@ -280,7 +345,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
       CU(cudaGetLastError());
       TRY(read_counters(s, &hc));
       arena_full = hc.error_flag == 1;
-    }
+    } else if (reg_first) hc.overflow_count = 0; // everything handed on was resolved by k_cand_pair
     if (!arena_full && hc.overflow_count) {
       // ---- big path: plan scratch slices on the host, run in rounds within the scratch limit ----
       const uint32_t n_over = hc.overflow_count;
@@ -343,7 +408,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     if (!arena_full) break;
     TRY(grow_arena(s));
     CU(cudaMemsetAsync(&dc->cand_count, 0, sizeof(unsigned long long), s.stream));
-    CU(cudaMemsetAsync(&dc->overflow_count, 0, sizeof(uint32_t), s.stream));
+    CU(cudaMemsetAsync(&dc->overflow_count, 0, 2 * sizeof(uint32_t), s.stream)); // and overflow_count2
     CU(cudaMemsetAsync(&dc->error_flag, 0, sizeof(int), s.stream));
   }
   s.n_cand = hc.cand_count;
