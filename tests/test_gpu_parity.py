@@ -27,6 +27,11 @@ CASES = [
     # the 32-bit coordinate's pads, the range filter) on nearly every read
     ("edges_e3_s3", [1500] * 70 + [400, 130, 99, 40], 0.1, 0.0, 900, 100, 3, 1, 12, 3, 0.0),
     ("edges_e5_s2", [2200] * 50, 0.3, 0.0, 600, 120, 5, 1, 11, 2, 0.0),
+    # dense indexes (window 8: 65 536 buckets, ~30 occurrences per seed as on the 3.1 Gbp configs): the occurrence runs
+    # fill k_cand_reg's register slots, some overflow them, and chance pairs of near entries survive in most groups
+    ("dense_q9", [2_500_000, 1_500_000], 0.0, 0.0, 300, 150, 7, 1, 8, 2, 0.0),
+    ("dense_q7", [2_200_000, 1_800_000], 0.02, 0.0, 300, 120, 5, 1, 8, 2, 0.0),
+    ("dense_q5", [1_200_000, 900_000], 0.05, 0.0, 300, 100, 3, 1, 8, 1, 0.0),
 ]
 
 
@@ -131,6 +136,23 @@ def test_candidates_pair_path_sizes(setup, bits, values, layout):
         setup.mapper.set_option("pair_layout", 0)
         setup.mapper.set_option("pair_bits", 0)
         setup.mapper.set_option("pair_values", 0)
+        setup.mapper.set_option("cand_mode", 0)
+
+
+@pytest.mark.parametrize("bits", [1024, 16384, 0])
+def test_candidates_reg_path(setup, bits):
+    """k_cand_reg (a group's entries in registers between the bitmap passes) forced whatever the index density
+    (cand_mode 5; shapes Q = 5, 7, 9, the others take k_cand_pair), then excluded (cand_mode 6: k_cand_pair alone).
+    A crowded bitmap floods the flagged list, so most read-strands go down the chain k_cand_reg -> k_cand_pair (list
+    mode, length read on the device) -> k_cand."""
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("pair_bits", bits)
+    try:
+        for mode in (5, 6):
+            setup.mapper.set_option("cand_mode", mode)
+            check_candidates(setup, seqs)
+    finally:
+        setup.mapper.set_option("pair_bits", 0)
         setup.mapper.set_option("cand_mode", 0)
 
 
