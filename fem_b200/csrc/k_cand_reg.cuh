@@ -34,28 +34,29 @@ __host__ __device__ inline size_t cand_reg_smem_bytes_per_warp(uint32_t M) {
   return (size_t)M / 8 * 2 + (PAIR_SC + 2 * PAIR_AC) * 8 + PAIR_FC * 8;
 }
 
-// Marks bitmap position h: A's word at shared address bmA_s + 4 * (h >> 5); B's word, bmB_off bytes behind it, when
-// the bit was already set.  `bit` is 0 for a slot without an entry, so the first atomic needs no predicate (ptxas
-// turns a predicated shared atomic into a divergence region: BSSY / BRA / ATOMS / BSYNC).
-template <int VARIANT>
-__device__ __forceinline__ void preg_mark(uint32_t bmA_s, uint32_t bmB_off, uint32_t h, bool valid) {
-  const uint32_t bit = valid ? 1u << (h & 31u) : 0u;
-  uint32_t addr;
-  asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 5;\n\tmad.lo.u32 %0, t, 4, %2;\n\t}" : "=r"(addr) : "r"(h), "r"(bmA_s));
-  uint32_t old;
-  asm volatile("atom.shared.or.b32 %0, [%1], %2;" : "=r"(old) : "r"(addr), "r"(bit) : "memory");
-  const uint32_t dup = old & bit;
-  if (VARIANT == 1) {
-    asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr + bmB_off), "r"(dup) : "memory");
-  } else if (VARIANT == 2) {
-    if (__any_sync(0xffffffffu, dup != 0)) asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr + bmB_off), "r"(dup) : "memory");
-  } else {
-    if (dup) asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr + bmB_off), "r"(dup) : "memory");
+// Bitmap marks of NS slots at once: A's word at shared address bmA_s + 4 * (h >> 5); B's word, bmB_off bytes behind it,
+// when the bit was already set.  All NS first atomics are issued before the first result is looked at (a shared atomic
+// returns after ~30 cycles; one at a time, the kernel waited on the short scoreboard for a third of its cycles).
+// A slot without an entry ORs 0 into the word its filler value points at -- the fillers differ from lane to lane, so
+// these no-ops do not pile up on one address -- and so needs no predicate: ptxas turns a predicated shared atomic into
+// a divergence region (BSSY / BRA / ATOMS / BSYNC).
+template <int NS>
+__device__ __forceinline__ void preg_mark(uint32_t bmA_s, uint32_t bmB_off, const uint32_t (&h)[NS], const uint32_t (&bit)[NS]) {
+  uint32_t addr[NS], old[NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 5;\n\tmad.lo.u32 %0, t, 4, %2;\n\t}" : "=r"(addr[i]) : "r"(h[i]), "r"(bmA_s));
+    asm volatile("atom.shared.or.b32 %0, [%1], %2;" : "=r"(old[i]) : "r"(addr[i]), "r"(bit[i]));
+  }
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    const uint32_t dup = old[i] & bit[i];
+    if (dup) asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr[i] + bmB_off), "r"(dup));
   }
 }
 
-template <int Q, int UA, int VARIANT>
-__global__ void __launch_bounds__(128) k_cand_reg(CandArgs A, uint32_t M) {
+template <int Q, int UA, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) {
   constexpr uint32_t R = Q - 1, LPR = 32u / R, UB = PREG_UB;
   static_assert(Q >= 2 && Q <= FEM_MAX_Q && UA % 4 == 0 && UA + UB <= 32, "shape");
   extern __shared__ uint64_t smem_reg[];
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(128) k_cand_reg(CandArgs A, uint32_t M) {
   const uint32_t a = (uint32_t)A.a, e32 = (uint32_t)A.e, mask = M - 1, wmask = M / 32 - 1;
   const uint64_t e = (uint64_t)A.e;
   const uint32_t myrun = lane / LPR, sub = lane - myrun * LPR;
+  const uint64_t filler = (uint64_t)(lane * 0x9E3779B1u); // lane-specific: the no-op atomics of empty slots spread over the words
   const bool runner = myrun < R;
   uint32_t na = 0;
   bool overflow = false;
@@ -114,12 +116,12 @@ __global__ void __launch_bounds__(128) k_cand_reg(CandArgs A, uint32_t M) {
     uint64_t o[UA], ob[UB];
 #pragma unroll
     for (int u = 0; u < UA; ++u) {
-      o[u] = 0;
+      o[u] = filler; // a slot without an entry: see preg_mark
       if ((int32_t)(u * LPR) < lim && (u > 0 || k0 >= 0)) o[u] = p0[u * LPR];
     }
 #pragma unroll
     for (int j = 0; j < (int)UB; ++j) {
-      ob[j] = 0;
+      ob[j] = filler;
       if (32 * j < limb) ob[j] = pb[32 * j];
     }
     // valid slots of this lane, as a mask: slots [k0 < 0, ceil(lim / LPR)) of runs 0..Q-2 (rounds <= UA was checked)
@@ -141,34 +143,46 @@ __global__ void __launch_bounds__(128) k_cand_reg(CandArgs A, uint32_t M) {
     mv = warp_max_u64(has ? mv : 0ull);
     __syncwarp();
     // ---- pass 1, runs 0..Q-2 ---------------------------------------------------------------------------
-    // A slot without an entry holds 0 and marks the bucket that value falls into like any entry the reference drops:
-    // a false flag at worst (its own flag is masked by vm), and no predicate on the way.
+    // Entries the reference drops (position < seed offset) are marked like the others: a false flag at worst.
     uint32_t hs[UA / 2 + 2]; // bitmap positions, two to a register: slots 0..UA-1, then the last run's
 #pragma unroll
     for (int c = 0; c < UA / 4; ++c) {
       hs[2 * c] = hs[2 * c + 1] = 0;
       if (4u * c < rounds) {
+        uint32_t h[4], bit[4];
 #pragma unroll
-        for (int u = 4 * c; u < 4 * c + 4; ++u) {
-          const uint32_t h = ((((uint32_t)o[u] - rst) >> 3) + (uint32_t)(o[u] >> 32) * 0x9E3779B1u) & mask;
-          preg_mark<VARIANT>(bmA_s, bmB_off, h, true);
-          hs[u >> 1] |= h << (16 * (u & 1));
+        for (int i = 0; i < 4; ++i) {
+          const int u = 4 * c + i;
+          h[i] = ((((uint32_t)o[u] - rst) >> 3) + (uint32_t)(o[u] >> 32) * 0x9E3779B1u) & mask;
+          bit[i] = ((vm >> u) & 1u) << (h[i] & 31u);
+          hs[u >> 1] |= h[i] << (16 * (u & 1));
         }
+        preg_mark<4>(bmA_s, bmB_off, h, bit);
       }
     }
     // ---- pass 1, last run: entries up to the maximum of the others (ascending: the rest lies beyond) ----------
     hs[UA / 2] = hs[UA / 2 + 1] = 0;
+    if (fl) {
+      uint32_t h[UB], bit[UB];
 #pragma unroll
-    for (int j = 0; j < (int)UB; ++j) {
-      if (32u * j < fl) {
+      for (int j = 0; j < (int)UB; ++j) {
         const uint32_t lo = (uint32_t)ob[j];
         const uint64_t v = ob[j] - stl;
-        const uint32_t h = (((uint32_t)v >> 3) + (uint32_t)(v >> 32) * 0x9E3779B1u) & mask;
+        h[j] = (((uint32_t)v >> 3) + (uint32_t)(v >> 32) * 0x9E3779B1u) & mask;
         const bool keep = 32 * j < limb && lo >= stl && v <= mv;
-        preg_mark<VARIANT>(bmA_s, bmB_off, h, keep);
+        bit[j] = keep ? 1u << (h[j] & 31u) : 0u;
         vm |= keep ? 1u << (UA + j) : 0u;
-        hs[(UA + j) >> 1] |= h << (16 * ((UA + j) & 1));
+        hs[(UA + j) >> 1] |= h[j] << (16 * ((UA + j) & 1));
       }
+      preg_mark<UB>(bmA_s, bmB_off, h, bit);
+    }
+    // the next group's seeds have arrived by now: pull its occurrence runs into L2 (128-byte lines, one per lane of a
+    // run, six for the last run) while this group is finished
+    if (g + 1 < A.step) {
+      const uint32_t qb = __shfl_sync(0xffffffffu, nb, myrun), qf = __shfl_sync(0xffffffffu, nfreq, myrun);
+      const uint32_t lb = __shfl_sync(0xffffffffu, nb, Q - 1), lf = __shfl_sync(0xffffffffu, nfreq, Q - 1);
+      if (runner && 16u * sub < qf + 15u) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.occ + qb + 16u * sub));
+      if (lane < 2u * UB && 16u * lane < lf + 15u) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.occ + lb + 16u * lane));
     }
     __syncwarp();
     // ---- flag map F = B | (A & (A rotated by one bucket either way)), four word pairs per lane and round --
@@ -194,12 +208,13 @@ __global__ void __launch_bounds__(128) k_cand_reg(CandArgs A, uint32_t M) {
           fm |= ((bmB[h >> 5] >> (h & 31u)) & 1u) << u;
         }
       }
+    if (fl) {
 #pragma unroll
-    for (int j = 0; j < (int)UB; ++j)
-      if (32u * j < fl) {
+      for (int j = 0; j < (int)UB; ++j) {
         const uint32_t h = (hs[(UA + j) >> 1] >> (16 * ((UA + j) & 1))) & 0xFFFFu;
         fm |= ((bmB[h >> 5] >> (h & 31u)) & 1u) << (UA + j);
       }
+    }
     fm &= vm;
     // ---- the flagged entries' values again (L1/L2 hits), filtered exactly ---------------------------------
     uint32_t nf = 0;

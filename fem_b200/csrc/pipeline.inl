@@ -267,11 +267,11 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   if (pl.pair32_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair32_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
   if (pl.pair_reg && pl.reg_smem > 48 * 1024) {
-    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
-    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
-    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
-    CU(cudaFuncSetAttribute(k_cand_reg<7, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
-    CU(cudaFuncSetAttribute(k_cand_reg<5, REG_UA, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<7, REG_UA, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
+    CU(cudaFuncSetAttribute(k_cand_reg<5, REG_UA, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
   }
 
   Counters hc;
@@ -288,12 +288,12 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (reg_first) {
       const unsigned grid = (unsigned)((n_rs + 3) / 4);
-      static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 0; // experiments: preg_mark
-      if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 1><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 2><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 9) k_cand_reg<9, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 7) k_cand_reg<7, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else k_cand_reg<5, REG_UA, 0><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 0; // experiments: resident blocks per SM
+      if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 8><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 7><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 9) k_cand_reg<9, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else if (pl.Q == 7) k_cand_reg<7, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      else k_cand_reg<5, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
       ++s.n_launches;
       // what it hands on goes to k_cand_pair without a trip to the host: the list's length is read on the device;
       // REG_CHAIN warps are launched, a longer list (seen below) gets a second launch for its tail
