@@ -227,6 +227,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char *b = getenv("FEM_BLOCKING_SYNC")) c->blocking_sync = atoi(b) != 0;
   if (const char *m = getenv("FEM_CAND_MODE")) { const int v = atoi(m); if (v >= 0 && v <= 6) c->cand_mode = v; } // experiments: see "cand_mode"
+  if (const char *m = getenv("FEM_PAIR_BITS")) { const int v = atoi(m); if (v >= 1024 && v <= 32768 && (v & (v - 1)) == 0) c->pair_bits = (uint32_t)v; } // experiments: see "pair_bits"
   if (const char *m = getenv("FEM_SMALL_SHAPE")) { const int v = atoi(m); if (v == 1 || v == 4) c->small_shape = v; } // experiments: see "small_shape"
   if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
   for (auto &s : c->slot) {

@@ -28,9 +28,6 @@
 #include "k_cand_pair.cuh" // PAIR_FC, PAIR_SC, PAIR_AC
 
 #define PREG_UB 3 // slots of the last run (32 entries each)
-#define PREG_T 128u                 // slots of the exact stage's table (at most PAIR_FC = 64 flagged entries)
-#define PREG_T_SHIFT 57u            // 64 - log2(PREG_T)
-#define PREG_TABLE_MIN_BITS 8192u   // the table (PREG_T * 12 bytes) lives in the two bitmaps' place: 2 * M / 8 bytes
 
 // M bits per bitmap (power of two, 1024..32768)
 __host__ __device__ inline size_t cand_reg_smem_bytes_per_warp(uint32_t M) {
@@ -219,76 +216,52 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
       }
     }
     fm &= vm;
-    // ---- the flagged entries' values again (L1/L2 hits), filtered exactly; a lane's entries go to consecutive places
-    //      of the flagged list (prefix sum of the lanes' counts).  An entry the reference drops (position < seed offset,
-    //      filter.c:89,106) leaves a filler no value lies within e of: record 2^32 - 1, positions 16 apart. ----------------
-    const uint32_t mine = __popc(fm);
-    uint32_t incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-      if ((int)lane >= d) incl += t;
+    // ---- the flagged entries' values again (L1/L2 hits), filtered exactly ---------------------------------
+    uint32_t nf = 0;
+    while (__any_sync(0xffffffffu, fm != 0)) {
+      bool keep = false;
+      uint64_t v = 0;
+      if (fm) {
+        const uint32_t u = (uint32_t)__ffs(fm) - 1u;
+        fm &= fm - 1;
+        if (u < (uint32_t)UA) {
+          const uint64_t x = p0[u * LPR];
+          keep = (uint32_t)x >= rst; // filter.c:89,106
+          v = x - rst;
+        } else {
+          v = pb[32u * (u - UA)] - stl; // kept in pass 1 already
+          keep = true;
+        }
+      }
+      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const uint32_t idx = nf + __popc(bal & lanemask_lt());
+        if (idx < PAIR_FC) fv[idx] = v;
+      }
+      nf += __popc(bal);
     }
-    const uint32_t nf = __shfl_sync(0xffffffffu, incl, 31);
     if (nf > PAIR_FC) { overflow = true; break; }
     if (nf < a + 1) continue; // a survivor needs a other flagged entries
-    for (uint32_t at = incl - mine; fm; ++at) {
-      const uint32_t u = (uint32_t)__ffs(fm) - 1u;
-      fm &= fm - 1;
-      const bool last_run = u >= (uint32_t)UA;
-      const uint64_t x = last_run ? pb[32u * (u - UA)] : p0[u * LPR];
-      const uint32_t sx = last_run ? stl : rst;
-      fv[at] = (uint32_t)x >= sx ? x - sx : 0xFFFFFFFF00000000ull | (at << 4);
-    }
     __syncwarp();
+    // ---- exact: flagged entries with at least a other flagged entries in [x, x+e] ----------------------
     uint32_t ns = 0;
-    if (M >= PREG_TABLE_MIN_BITS) {
-      // ---- exact, by a small table in the bitmaps' place (they are done for this group): value -> multiplicity, open
-      //      addressing by 8-wide bucket as in k_cand_hash; x survives iff its bucket and the next hold at least a + 1
-      //      entries in [x, x+e] (its own copies included).  O(flagged) instead of the all-pairs count below. ---------------
-      uint64_t *tab = reinterpret_cast<uint64_t *>(bmA);
-      uint32_t *tcn = reinterpret_cast<uint32_t *>(tab + PREG_T);
-      for (uint32_t t = lane; t < PREG_T; t += 32) { tab[t] = FEM_SENTINEL; tcn[t] = 0; }
-      __syncwarp();
-      for (uint32_t t = lane; t < nf; t += 32) table_insert(tab, tcn, PREG_T - 1, PREG_T_SHIFT, fv[t]);
-      __syncwarp();
-      for (uint32_t t0 = 0; t0 < nf; t0 += 32) {
-        const uint32_t idx = t0 + lane;
-        uint64_t xv = 0;
-        bool keep = false;
-        if (idx < nf) {
-          xv = fv[idx];
-          const uint32_t cnt = table_count(tab, tcn, PREG_T - 1, PREG_T_SHIFT, xv >> 3, xv, e) +
-                               table_count(tab, tcn, PREG_T - 1, PREG_T_SHIFT, (xv >> 3) + 1, xv, e);
-          keep = cnt >= a + 1; // cnt includes the entry itself
-        }
-        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-          const uint32_t k = ns + __popc(bal & lanemask_lt());
-          if (k < PAIR_SC) surv[k] = xv;
-        }
-        ns += __popc(bal);
-      }
-    } else {
-      // ---- exact: flagged entries with at least a other flagged entries in [x, x+e] (bitmaps too small for the table) ----
-      for (uint32_t t0 = 0; t0 < nf; t0 += 32) {
-        const uint32_t idx = t0 + lane;
-        const uint64_t xv = idx < nf ? fv[idx] : FEM_SENTINEL;
-        const uint32_t xlo = (uint32_t)xv, xhi = (uint32_t)(xv >> 32);
-        uint32_t cnt = 0;
+    for (uint32_t t0 = 0; t0 < nf; t0 += 32) {
+      const uint32_t idx = t0 + lane;
+      const uint64_t xv = idx < nf ? fv[idx] : FEM_SENTINEL;
+      const uint32_t xlo = (uint32_t)xv, xhi = (uint32_t)(xv >> 32);
+      uint32_t cnt = 0;
 #pragma unroll 4
-        for (uint32_t j = 0; j < nf; ++j) {
-          const uint64_t y = fv[j];
-          cnt += ((uint32_t)y - xlo <= e32 && (uint32_t)(y >> 32) == xhi) ? 1u : 0u;
-        }
-        const bool keep = idx < nf && cnt >= a + 1; // cnt includes the entry itself
-        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-          const uint32_t k = ns + __popc(bal & lanemask_lt());
-          if (k < PAIR_SC) surv[k] = ((uint64_t)xhi << 32) | xlo;
-        }
-        ns += __popc(bal);
+      for (uint32_t j = 0; j < nf; ++j) {
+        const uint64_t y = fv[j];
+        cnt += ((uint32_t)y - xlo <= e32 && (uint32_t)(y >> 32) == xhi) ? 1u : 0u;
       }
+      const bool keep = idx < nf && cnt >= a + 1; // cnt includes the entry itself
+      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const uint32_t k = ns + __popc(bal & lanemask_lt());
+        if (k < PAIR_SC) surv[k] = ((uint64_t)xhi << 32) | xlo;
+      }
+      ns += __popc(bal);
     }
     if (ns > PAIR_SC) { overflow = true; break; }
     if (ns == 0) continue;

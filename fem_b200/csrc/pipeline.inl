@@ -288,7 +288,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (reg_first) {
       const unsigned grid = (unsigned)((n_rs + 3) / 4);
-      static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 1; // experiments: resident blocks per SM (1: 8 blocks of 64 registers, measured best)
+      static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 1; // experiments: resident blocks per SM (1: 8 blocks of 64 registers, measured best: 14.5 against 15.0 ms)
       if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 8><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
       else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 7><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
       else if (pl.Q == 9) k_cand_reg<9, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
