@@ -121,6 +121,21 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
       for (int g = (int)lane; g < step; g += 32) {
         const int n_g = (n_s - g) / step;
         const int W = n_g - Q * s + 1; // real columns 1..W (>= 1 by the feasibility check)
+        if (W == 1) {
+          // zero slack (cfg3: 27 seeds per group for 9 x 3): the table is one column wide and the selection is forced --
+          // seed r is the group's q-gram (r - 1) * s; a row whose sum reaches "infinity" ends the reference's traceback
+          // (column 0), exactly as in the general form below
+          uint32_t sum = 0;
+          for (int r = 1; r <= Q; ++r) {
+            const int q = g + (r - 1) * s * step;
+            uint32_t v = sum + sm_freq[q];
+            if (A.inf <= v) { v = A.inf; bad = true; }
+            sum = v;
+            sel[g * Q + (Q - r)] = (uint16_t)q;
+          }
+          before += sum;
+          continue;
+        }
         uint32_t *M = m_rows + (size_t)g * (w_max + 1);
         uint16_t *am = amin + (size_t)g * Q * w_max;
         for (int c = 0; c <= W; ++c) M[c] = 0; // row 0 (column 0 unused)
