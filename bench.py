@@ -357,7 +357,8 @@ def run_ours(args):
     def reduce_ranks(x, op="max"):
         if dist is None:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        # the device by name: the single-process leg below leaves another device current on rank 0's thread
+        t = torch.tensor([x], dtype=torch.float64, device=torch.device("cuda", local_rank))
         dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
         return float(t.item())
 
@@ -481,6 +482,7 @@ def run_ours(args):
             except Exception as ex:  # the leg is reported, never fatal for the line
                 sp = {"value": None, "error": repr(ex)[:300]}
         cpu_barrier()
+        torch.cuda.set_device(local_rank)
         if rank == 0:
             forms["single_process"] = sp
     if os.path.exists(out):
