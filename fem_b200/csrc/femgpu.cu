@@ -18,7 +18,6 @@
 #include "k_cand.cuh"
 #include "k_cand_hash.cuh"
 #include "k_cand_pair.cuh"
-#include "k_cand_pair32.cuh"
 #include "k_cand_reg.cuh"
 #include "k_cand_small.cuh"
 #include "k_index.cuh"
@@ -167,11 +166,6 @@ struct femgpu_ctx {
   size_t smem_optin = 0;
   // index
   DBuf lut, occ;
-  DBuf occ32, gbase, padflag; // k_cand_pair32's 32-bit copy of occ (occ32.inl)
-  bool occ32_ok = false;
-  bool occ32_tried = false;   // derive_occ32 ran for the resident index + reference
-  int pair_layout = 0;        // 0 / 64: k_cand_pair on the occurrence table itself; 32: k_cand_pair32 on the
-                              // 32-bit copy (derived on first use; half the DRAM bytes, measured slower on cfg3)
   uint64_t n_occ = 0;
   int idx_k = 0, idx_step = 0;
   // reference
@@ -262,7 +256,7 @@ extern "C" void femgpu_destroy(femgpu_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto &s : c->slot) slot_release(s);
-  c->lut.release(); c->occ.release(); c->occ32.release(); c->gbase.release(); c->padflag.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
+  c->lut.release(); c->occ.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
   delete c;
 }
 
@@ -276,7 +270,6 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "l2_persist_lut") c->l2_persist_lut = value != 0;
   else if (k == "cand_mode" && value >= 0 && value <= 6) c->cand_mode = (int)value;
   else if (k == "small_shape" && (value == 0 || value == 1 || value == 4)) c->small_shape = (int)value;
-  else if (k == "pair_layout" && (value == 0 || value == 32 || value == 64)) c->pair_layout = (int)value;
   else if (k == "pair_bits" && (value == 0 || (value >= 1024 && value <= 32768 && (value & (value - 1)) == 0))) c->pair_bits = (uint32_t)value;
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
@@ -333,10 +326,7 @@ extern "C" int femgpu_measure_int32_peak(femgpu_ctx *c, double giops[3]) {
   return 0;
 }
 
-static int derive_occ32(femgpu_ctx *c);
-static int derive_occ32_now(femgpu_ctx *c);
 #include "upload.inl"
 #include "pipeline.inl"
 #include "index_build.inl"
-#include "occ32.inl"
 #include "api.inl"

@@ -28,7 +28,7 @@ extern "C" int femgpu_build_index(femgpu_ctx *c, int32_t k, int32_t step) {
   };
 #define TRYC(x) do { int rc__ = (x); if (rc__) return cleanup(rc__); } while (0)
 #define CUC(call) do { cudaError_t err__ = (call); if (err__ != cudaSuccess) return cleanup(set_error(err__ == cudaErrorMemoryAllocation ? FEMGPU_ENOMEM : FEMGPU_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(err__), __FILE__, __LINE__)); } while (0)
-  c->n_occ = 0; c->idx_k = 0; c->idx_step = 0; c->occ32_ok = false; // no index until the build has finished
+  c->n_occ = 0; c->idx_k = 0; c->idx_step = 0; // no index until the build has finished
   TRYC(c->lut.reserve(lut_n * sizeof(uint32_t)));
   TRYC(c->occ.reserve(std::max<uint64_t>(n, 1) * sizeof(uint64_t) + 64));
   TRYC(d_sbase.reserve((n_rec + 1) * 8));
@@ -108,7 +108,7 @@ extern "C" int femgpu_build_index(femgpu_ctx *c, int32_t k, int32_t step) {
   c->n_occ = n;
   c->idx_k = k;
   c->idx_step = step;
-  return derive_occ32(c);
+  return 0;
 }
 
 extern "C" int femgpu_index_sizes(const femgpu_ctx *c, size_t *lut_n, size_t *occ_n) {

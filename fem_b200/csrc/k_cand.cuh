@@ -20,8 +20,6 @@
 
 struct CandArgs {
   const uint64_t *occ;
-  // 32-bit copy of occ in a padded global coordinate (k_cand_pair32.cuh); nullptr when it does not fit
-  const uint32_t *occ32, *gbase, *padflag;
   uint32_t n_rec;
   const uint32_t *seed_begin, *seed_freq, *seed_start; // [rs*step+g][Q]
   const uint8_t *rs_status;

@@ -13,8 +13,7 @@ struct Plan { // derived from params + the batch
   uint32_t hash_T, hash_shift; // k_cand_hash: table slots per warp, 64 - log2(slots)
   size_t hash_smem;
   uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
-  size_t pair_smem, pair32_smem, reg_smem;
-  bool pair32;
+  size_t pair_smem, reg_smem;
   bool pair_reg; // k_cand_reg first (shape instantiated for this Q and runs expected to fit its slots)
   int first_path; // 0 sort, 1 hash, 2 pair, 3 small
   size_t small_smem;
@@ -94,9 +93,6 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     pl->pair_shift = 32;
     for (uint32_t t = M; t > 1; t >>= 1) --pl->pair_shift;
     pl->pair_smem = 4 * cand_pair_smem_bytes_per_warp(M, VC);
-    pl->pair32_smem = 4 * cand_pair32_smem_bytes_per_warp(M, VC + 64);
-    if (c->pair_layout == 32 && !c->occ32_tried) TRY(derive_occ32_now(c));
-    pl->pair32 = c->occ32_ok && c->pair_layout == 32;
   }
   pl->first_path = c->cand_mode == 1 ? 0 : c->cand_mode == 2 ? 1 : (pl->a >= 1 ? 2 : 1);
   {
@@ -108,7 +104,7 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     const bool shape = pl->Q == 5 || pl->Q == 7 || pl->Q == 9;
     const bool fits = mean + 3.3 * std::sqrt(mean) + 1.0 <= (double)(REG_UA * lpr - 3) && mean + 6.0 * std::sqrt(mean) <= 32.0 * PREG_UB;
     pl->reg_smem = 4 * cand_reg_smem_bytes_per_warp(pl->pair_M);
-    pl->pair_reg = pl->a >= 1 && shape && !pl->pair32 && c->cand_mode != 6 && (c->cand_mode == 5 || ((c->cand_mode == 0 || c->cand_mode == 3) && fits)) &&
+    pl->pair_reg = pl->a >= 1 && shape && c->cand_mode != 6 && (c->cand_mode == 5 || ((c->cand_mode == 0 || c->cand_mode == 3) && fits)) &&
                    pl->reg_smem <= c->smem_optin;
     if (c->cand_mode == 5 || c->cand_mode == 6) pl->first_path = pl->a >= 1 ? 2 : 1;
   }
@@ -249,9 +245,6 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.rs_status = sa.rs_status;
   ca.read_off = sa.read_off;
   ca.rec_len = c->rec_len.as<uint32_t>();
-  ca.occ32 = c->occ32_ok ? c->occ32.as<uint32_t>() : nullptr;
-  ca.gbase = c->gbase.as<uint32_t>();
-  ca.padflag = c->padflag.as<uint32_t>();
   ca.n_rec = c->n_rec;
   ca.n_rs = (uint32_t)n_rs;
   ca.step = pl.step; ca.e = pl.e; ca.a = pl.a; ca.Q = pl.Q;
@@ -264,7 +257,6 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   ca.S = c->sort_capacity; ca.Acap = c->acc_capacity;
   if (pl.cand_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.cand_smem));
   if (pl.hash_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_hash, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.hash_smem));
-  if (pl.pair32_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair32_smem));
   if (pl.pair_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_cand_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.pair_smem));
   if (pl.pair_reg && pl.reg_smem > 48 * 1024) {
     CU(cudaFuncSetAttribute(k_cand_reg<9, REG_UA, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.reg_smem));
@@ -285,7 +277,6 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     const bool reg_first = pl.first_path == 2 && pl.pair_reg;
     if (pl.first_path == 3 && pl.small_R == 1) k_cand_small<1><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
     else if (pl.first_path == 3) k_cand_small<4><<<(unsigned)((n_rs + 3) / 4), 128, pl.small_smem, s.stream>>>(ca, pl.small_inv_Q);
-    else if (pl.first_path == 2 && pl.pair32) k_cand_pair32<<<(unsigned)((n_rs + 3) / 4), 128, pl.pair32_smem, s.stream>>>(ca, pl.pair_M, pl.pair_VC + 64);
     else if (reg_first) {
       const unsigned grid = (unsigned)((n_rs + 3) / 4);
       static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 1; // experiments: resident blocks per SM (1: 8 blocks of 64 registers, measured best: 14.5 against 15.0 ms)

@@ -42,7 +42,7 @@ extern "C" int femgpu_upload_index(femgpu_ctx *c, int32_t k, int32_t step, const
   c->n_occ = occ_n;
   c->idx_k = k;
   c->idx_step = step;
-  return derive_occ32(c);
+  return 0;
 }
 
 extern "C" int femgpu_upload_index_file(femgpu_ctx *c, const char *path) {
@@ -95,7 +95,7 @@ extern "C" int femgpu_upload_index_file(femgpu_ctx *c, const char *path) {
   c->n_occ = occ_n;
   c->idx_k = k;
   c->idx_step = step;
-  return derive_occ32(c);
+  return 0;
 }
 
 extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char *const *bases, const uint32_t *lens) {
@@ -156,7 +156,7 @@ extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char
   c->ref_total = total;
   c->ref_has_n = (any_n & 1) != 0;
   c->ref_canonical = (any_n & 2) == 0;
-  return derive_occ32(c);
+  return 0;
 }
 
 // The resident index, reference and record names of `src` copied device to device (NVLink peer copies
@@ -202,5 +202,5 @@ extern "C" int femgpu_clone_resident(femgpu_ctx *dst, const femgpu_ctx *src) {
   dst->ref_has_n = src->ref_has_n;
   dst->ref_canonical = src->ref_canonical;
   dst->have_rnames = src->have_rnames;
-  return derive_occ32(dst);
+  return 0;
 }

@@ -144,9 +144,9 @@ void femgpu_free_pinned(void *p);
  * "acc_capacity", "l2_persist_lut", "seed_dp_mode" (0 automatic, 1 lane per group, 2 warp scan, 3 lane per group with several read-strands per warp),
  * "cand_mode" (0 automatic: near-pair path when a >= 1, hash path when a = 0; 1 sort path only;
  * 2 hash path first; 3 near-pair path first; 4 all-groups-at-once path first, the automatic
- * choice on sparse indexes), "small_shape" (k_cand_small: 0 automatic, 1 one seed per lane when step x Q <= 32,
- * 4 up to 128 seeds), "hash_slots", "pair_bits", "pair_values" (0 automatic), "pair_layout" (32: the near-pair path reads a
- * 32-bit copy of the occurrence table, derived on first use; 0 / 64: the table itself),
+ * choice on sparse indexes; 5 the near-pair path's register form (k_cand_reg) whatever the index density;
+ * 6 the near-pair path without its register form), "small_shape" (k_cand_small: 0 automatic, 1 one seed per lane
+ * when step x Q <= 32, 4 up to 128 seeds), "hash_slots", "pair_bits", "pair_values" (0 automatic),
  * "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 

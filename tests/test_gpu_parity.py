@@ -120,20 +120,17 @@ def test_candidates_hash_path_table_sizes(setup, slots):
         setup.mapper.set_option("cand_mode", 0)
 
 
-@pytest.mark.parametrize("layout", [32, 64])
 @pytest.mark.parametrize("bits,values", [(1024, 32), (1024, 2048), (4096, 128), (32768, 512), (0, 0)])
-def test_candidates_pair_path_sizes(setup, bits, values, layout):
+def test_candidates_pair_path_sizes(setup, bits, values):
     """k_cand_pair from a crowded bitmap (nearly every entry falsely flagged, most read-strands handed
     on to the sort path) and a tiny value buffer to generous ones; (0, 0) is the automatic plan."""
     seqs = [r[1] for r in setup.reads]
     setup.mapper.set_option("pair_bits", bits)
     setup.mapper.set_option("pair_values", values)
-    setup.mapper.set_option("pair_layout", layout)  # 32: the 32-bit copy of the occurrence table, 64: the table itself
-    setup.mapper.set_option("cand_mode", 3)
+    setup.mapper.set_option("cand_mode", 6)  # k_cand_pair itself (3 would take its register form where the shape fits)
     try:
         check_candidates(setup, seqs)
     finally:
-        setup.mapper.set_option("pair_layout", 0)
         setup.mapper.set_option("pair_bits", 0)
         setup.mapper.set_option("pair_values", 0)
         setup.mapper.set_option("cand_mode", 0)
