@@ -122,7 +122,7 @@ struct Slot {
   DBuf seed_begin, seed_freq, seed_start;
   DBuf rs_cand_first, rs_cand_count, rs_map_count, rs_map_first, block_sums;
   DBuf cand, cand_rs, result, maps, overflow_list, overflow_list2, counters;
-  DBuf read_flags, map_rs, aln;
+  DBuf read_flags, map_rs, aln, planes, rs_has_n;
   DBuf big_list, big_off, big_S, big_A, scratch, hash_list;
   DBuf cand_sorted, rs_cand_sorted_first; // femgpu_candidates_batch only
   // SAM text on the device (k_sam): inputs of the batch, per-read sizes / offsets / flags, the text
@@ -170,6 +170,7 @@ struct femgpu_ctx {
   int idx_k = 0, idx_step = 0;
   // reference
   DBuf ref2, refn, rec_base, rec_len;
+  DBuf refp0, refp1;          // bit planes of ref2 (k_ref_planes): bit 0 / bit 1 of the base codes, 32 bases per word
   DBuf rnames, rname_off;     // record names for k_sam (femgpu_set_reference_names)
   bool have_rnames = false;
   uint32_t n_rec = 0;
@@ -188,6 +189,7 @@ struct femgpu_ctx {
                         // 6: pair path first, never its register form
   uint32_t pair_bits = 0, pair_values = 0; // 0 automatic (from the index density)
   uint32_t hash_slots = 0; // 0 automatic (from the index density), else a power of two 32..4096
+  int verify_planes = 1; // k_verify: bit-plane form of the columns for candidates without ambiguous bases (0: general form only)
   int device_traceback = 1; // k_trace after compaction (0: the host computes every alignment)
   int blocking_sync = 0; // host waits sleep on an event instead of spinning in cudaStreamSynchronize (small hosts, one process per GPU)
   int seed_dp_mode = 0; // 0 automatic, 1 one lane per group, 2 warp scan, 3 several read-strands per warp (tests force each)
@@ -221,6 +223,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
   c->smem_optin = prop.sharedMemPerBlockOptin;
   if (const char *b = getenv("FEM_BLOCKING_SYNC")) c->blocking_sync = atoi(b) != 0;
   if (const char *m = getenv("FEM_CAND_MODE")) { const int v = atoi(m); if (v >= 0 && v <= 6) c->cand_mode = v; } // experiments: see "cand_mode"
+  if (const char *m = getenv("FEM_VERIFY_PLANES")) c->verify_planes = atoi(m) != 0; // experiments: see "verify_planes"
   if (const char *m = getenv("FEM_PAIR_BITS")) { const int v = atoi(m); if (v >= 1024 && v <= 32768 && (v & (v - 1)) == 0) c->pair_bits = (uint32_t)v; } // experiments: see "pair_bits"
   if (const char *m = getenv("FEM_SMALL_SHAPE")) { const int v = atoi(m); if (v == 1 || v == 4) c->small_shape = v; } // experiments: see "small_shape"
   if (const char *m = getenv("FEM_SEED_DP_MODE")) c->seed_dp_mode = atoi(m) >= 0 && atoi(m) <= 3 ? atoi(m) : 0; // experiments: see "seed_dp_mode"
@@ -239,7 +242,7 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
 static void slot_release(Slot &s) {
   DBuf *d[] = {&s.bases, &s.read_off, &s.codes, &s.rs_status, &s.rs_before, &s.rs_max_f, &s.rs_sum_f, &s.seed_begin,
                &s.seed_freq, &s.seed_start, &s.rs_cand_first, &s.rs_cand_count, &s.rs_map_count, &s.rs_map_first,
-               &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.overflow_list2, &s.counters, &s.big_list,
+               &s.block_sums, &s.read_flags, &s.map_rs, &s.aln, &s.planes, &s.rs_has_n, &s.cand, &s.cand_rs, &s.result, &s.maps, &s.overflow_list, &s.overflow_list2, &s.counters, &s.big_list,
                &s.big_off, &s.big_S, &s.big_A, &s.scratch, &s.hash_list, &s.cand_sorted, &s.rs_cand_sorted_first,
                &s.names, &s.name_off, &s.quals, &s.has_qual, &s.sam_bytes, &s.sam_host, &s.sam_off, &s.sam_blocks, &s.sam_text,
                &s.sam_big_list, &s.sam_big_ord, &s.sam_big_rec_off};
@@ -256,7 +259,7 @@ extern "C" void femgpu_destroy(femgpu_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto &s : c->slot) slot_release(s);
-  c->lut.release(); c->occ.release(); c->ref2.release(); c->refn.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
+  c->lut.release(); c->occ.release(); c->ref2.release(); c->refn.release(); c->refp0.release(); c->refp1.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
   delete c;
 }
 
@@ -274,6 +277,7 @@ extern "C" int femgpu_set_option(femgpu_ctx *c, const char *key, int64_t value) 
   else if (k == "pair_values" && (value == 0 || (value >= 32 && value <= 4096 && value % 2 == 0))) c->pair_values = (uint32_t)value;
   else if (k == "hash_slots" && (value == 0 || (value >= 32 && value <= 4096 && (value & (value - 1)) == 0))) c->hash_slots = (uint32_t)value;
   else if (k == "device_traceback") c->device_traceback = value != 0;
+  else if (k == "verify_planes") c->verify_planes = value != 0;
   else if (k == "blocking_sync" && (value == 0 || value == 1)) c->blocking_sync = (int)value;
   else if (k == "seed_dp_mode" && value >= 0 && value <= 3) c->seed_dp_mode = (int)value;
   else return set_error(FEMGPU_EINVAL, "unknown option or bad value: %s=%lld", key, (long long)value);
@@ -326,6 +330,7 @@ extern "C" int femgpu_measure_int32_peak(femgpu_ctx *c, double giops[3]) {
   return 0;
 }
 
+static int derive_ref_planes(femgpu_ctx *c);
 #include "upload.inl"
 #include "pipeline.inl"
 #include "index_build.inl"

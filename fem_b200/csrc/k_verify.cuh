@@ -25,7 +25,51 @@ struct VerifyArgs {
   uint32_t *result;            // out per candidate: dist<<16 | end_offset, or 0xFFFFFFFF
   uint32_t *rs_map_count;      // out per read-strand (atomic)
   unsigned long long *cols_executed; // out: Myers columns actually computed (roofline accounting)
+  // bit planes (k_planes / k_ref_planes): bit 0 and bit 1 of the base codes, one bit per base, 32 bases per word
+  const uint32_t *refp0, *refp1;     // reference (nullptr: not derived -> general form)
+  const uint32_t *planes;            // reads: per read-strand [3][plane_words]: bit 0, bit 1, "is N"
+  uint32_t plane_words;              // words per plane = ceil(l_max / 32)
+  const uint8_t *rs_has_n;           // per read-strand: some base is ambiguous (general form)
 };
+
+// ---- bit planes ----------------------------------------------------------------------------------------
+// Reads: one warp per read-strand; 32 codes per round, a ballot per plane.
+__global__ void __launch_bounds__(256) k_planes(const uint8_t *codes, const uint64_t *read_off, uint32_t n_rs, uint32_t plane_words,
+                                                uint32_t *planes, uint8_t *rs_has_n) {
+  const uint32_t lane = lane_id();
+  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (rs >= n_rs) return;
+  const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
+  const uint64_t off = read_off[read];
+  const uint32_t l = (uint32_t)(read_off[read + 1] - off);
+  const uint8_t *text = codes + 2 * off + (uint64_t)dir * l;
+  uint32_t *out = planes + rs * 3ull * plane_words;
+  uint32_t any_n = 0;
+  for (uint32_t w = 0; w < plane_words; ++w) {
+    const uint32_t i = 32u * w + lane;
+    const uint32_t c = i < l ? text[i] : 0u;
+    const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1u), b1 = __ballot_sync(0xffffffffu, c & 2u), bn = __ballot_sync(0xffffffffu, c & 4u);
+    any_n |= bn;
+    if (lane == 0) { out[w] = b0; out[plane_words + w] = b1; out[2 * plane_words + w] = bn; }
+  }
+  if (lane == 0) rs_has_n[rs] = any_n != 0;
+}
+
+// Reference: plane word j (bases 32 j .. 32 j + 31) from the two 2-bit words ref2[2 j], ref2[2 j + 1].
+__device__ __forceinline__ uint32_t even_bits16(uint32_t x) { // bits 0, 2, 4, ... of x gathered into the low 16 bits
+  x &= 0x55555555u;
+  x = (x | (x >> 1)) & 0x33333333u;
+  x = (x | (x >> 2)) & 0x0F0F0F0Fu;
+  x = (x | (x >> 4)) & 0x00FF00FFu;
+  return (x | (x >> 8)) & 0xFFFFu;
+}
+__global__ void __launch_bounds__(256) k_ref_planes(const uint32_t *ref2, uint64_t n_words, uint32_t *p0, uint32_t *p1) {
+  const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_words) return;
+  const uint32_t a = ref2[2 * j], b = ref2[2 * j + 1];
+  p0[j] = even_bits16(a) | (even_bits16(b) << 16);
+  p1[j] = even_bits16(a >> 1) | (even_bits16(b >> 1) << 16);
+}
 
 template <bool HAS_N>
 __device__ __forceinline__ uint32_t ref_code_at(const DevRef &R, uint64_t g, uint32_t &w2, uint32_t &wn, bool reload) {
@@ -71,21 +115,13 @@ struct RefCursor {
   }
 };
 
+// One candidate in the general form: base codes one at a time, five Peq rows (ambiguous bases in the read or the
+// reference).  Leaves VP, VN and the bottom-cell error count of the last column, or dead.
 template <bool HAS_N>
-__global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
-  const uint64_t ci = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (ci >= A.n_cand) return; // grid tail only: whole warps or the last partial one
-  const uint32_t rs = A.cand_rs[ci];
-  const uint32_t j = (uint32_t)(ci - A.rs_cand_first[rs]), n = A.rs_cand_count[rs];
-  const uint32_t wmask = j < (n & ~7u) ? 0xFFFFu : 0xFFFFFFFFu; // align.c:12-13
-  const uint32_t read = rs >> 1, dir = rs & 1;
-  const uint64_t off = A.read_off[read];
-  const int l = (int)(A.read_off[read + 1] - off);
-  const uint8_t *text = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
-  const uint64_t cand = A.cand[ci];
-  const int e = A.e;
+__device__ __forceinline__ void verify_columns_general(const VerifyArgs &A, uint64_t g0, const uint8_t *text, int l, int e, uint32_t wmask,
+                                                       uint32_t &VP_out, uint32_t &VN_out, int &err_out, int &cols_out, bool &dead_out) {
   RefCursor<HAS_N> ref;
-  ref.seek(A.ref, A.ref.rec_base[cand >> 32] + (uint32_t)cand);
+  ref.seek(A.ref, g0);
 
   uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0; // Peq rows
   for (int i = 0; i < 2 * e; ++i) {                // align.c:104-107
@@ -115,6 +151,93 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
     if (err > 3 * e) { dead = true; cols = i + 1; break; }
     p0 >>= 1; p1 >>= 1; p2 >>= 1; p3 >>= 1; p4 >>= 1;
   }
+  VP_out = VP; VN_out = VN; err_out = err; cols_out = cols; dead_out = dead;
+}
+
+// The same columns for a candidate without ambiguous bases on either side, from bit planes: at column i the Peq
+// row of read base t, restricted to the band, is the set of j in [0, 2e] with reference[i + j] == t, i.e.
+//   ~((R0 >> i) ^ T0) & ~((R1 >> i) ^ T1) & band      R0/R1: planes of the window, T0/T1: bit 0 / bit 1 of t, replicated
+// -- two funnel shifts of the window planes, two predicated complements, one LOP3, instead of five conditional ORs, five
+// shifts, a byte load and a four-way select per column.  32 columns per round (one word of each read plane); the
+// bottom-cell bits of D0 are collected by a funnel shift and counted once per eight columns (the early exit of
+// align.c:128-130 only ever turns a candidate into a rejected one, and the count never decreases, so testing it
+// later changes nothing but the number of columns computed).
+__device__ __forceinline__ void verify_columns_planes(const VerifyArgs &A, uint64_t g0, const uint32_t *q, int l, int e, uint32_t wmask,
+                                                      uint32_t &VP_out, uint32_t &VN_out, int &err_out, int &cols_out, bool &dead_out) {
+  const uint32_t band = (2u << (2 * e)) - 1u;
+  const uint32_t *r0p = A.refp0 + (g0 >> 5), *r1p = A.refp1 + (g0 >> 5);
+  const uint32_t s0 = (uint32_t)g0 & 31u;
+  uint32_t VP = 0, VN = 0;
+  int err = 0, cols = l;
+  bool dead = false;
+  // window planes of the current round: bits [32 r, 32 r + 64) of the window, refilled word by word
+  uint32_t a0 = __funnelshift_r(__ldg(r0p), __ldg(r0p + 1), s0), a1 = __funnelshift_r(__ldg(r1p), __ldg(r1p + 1), s0);
+  const int three_e = 3 * e;
+#define FEM_COLUMN(ii)                                                                                   \
+  {                                                                                                        \
+    uint32_t u0 = __funnelshift_r(a0, b0, ii), u1 = __funnelshift_r(a1, b1, ii);                           \
+    if (t0 & (1u << (ii))) u0 = ~u0;                                                                       \
+    if (t1 & (1u << (ii))) u1 = ~u1;                                                                       \
+    uint32_t X = (~(u0 | u1) & band) | VN;                                                                 \
+    const uint32_t D0 = ((((VP + (X & VP)) & wmask) ^ VP) | X);                                            \
+    const uint32_t HP = VN | (~(VP | D0) & wmask);                                                         \
+    X = D0 >> 1;                                                                                           \
+    VP = (VP & D0) | (~(X | HP) & wmask);                                                                  \
+    VN = X & HP;                                                                                           \
+    d0bits = __funnelshift_r(d0bits, D0, 1);                                                               \
+  }
+  int i0 = 0;
+  for (; i0 + 32 <= l; i0 += 32) {
+    const int w = i0 >> 5;
+    const uint32_t b0 = __funnelshift_r(__ldg(r0p + w + 1), __ldg(r0p + w + 2), s0), b1 = __funnelshift_r(__ldg(r1p + w + 1), __ldg(r1p + w + 2), s0);
+    const uint32_t t0 = q[w], t1 = q[A.plane_words + w];
+    uint32_t d0bits = 0;
+#pragma unroll
+    for (int oct = 0; oct < 4; ++oct) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) FEM_COLUMN(8 * oct + k)
+      // d0bits holds the matches of the round's columns so far in its top 8 (oct + 1) bits
+      if (err + 8 * (oct + 1) - __popc(d0bits) > three_e) { dead = true; cols = i0 + 8 * (oct + 1); break; }
+    }
+    if (dead) break;
+    err += 32 - __popc(d0bits);
+    a0 = b0; a1 = b1;
+  }
+  if (!dead && i0 < l) { // the last, partial round: columns one at a time
+    const int w = i0 >> 5;
+    const uint32_t b0 = __funnelshift_r(__ldg(r0p + w + 1), __ldg(r0p + w + 2), s0), b1 = __funnelshift_r(__ldg(r1p + w + 1), __ldg(r1p + w + 2), s0);
+    const uint32_t t0 = q[w], t1 = q[A.plane_words + w];
+    for (int ii = 0; i0 + ii < l; ++ii) {
+      uint32_t d0bits = 0;
+      FEM_COLUMN(ii)
+      err += 1 - (int)(d0bits >> 31);
+      if (err > three_e) { dead = true; cols = i0 + ii + 1; break; }
+    }
+  }
+#undef FEM_COLUMN
+  VP_out = VP; VN_out = VN; err_out = err; cols_out = cols; dead_out = dead;
+}
+
+template <bool HAS_N>
+__global__ void __launch_bounds__(256) k_verify(VerifyArgs A) {
+  const uint64_t ci = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= A.n_cand) return; // grid tail only: whole warps or the last partial one
+  const uint32_t rs = A.cand_rs[ci];
+  const uint32_t j = (uint32_t)(ci - A.rs_cand_first[rs]), n = A.rs_cand_count[rs];
+  const uint32_t wmask = j < (n & ~7u) ? 0xFFFFu : 0xFFFFFFFFu; // align.c:12-13
+  const uint32_t read = rs >> 1, dir = rs & 1;
+  const uint64_t off = A.read_off[read];
+  const int l = (int)(A.read_off[read + 1] - off);
+  const uint64_t cand = A.cand[ci];
+  const int e = A.e;
+  const uint64_t g0 = A.ref.rec_base[cand >> 32] + (uint32_t)cand;
+  uint32_t VP, VN;
+  int err, cols;
+  bool dead;
+  if (!HAS_N && A.refp0 && !A.rs_has_n[rs])
+    verify_columns_planes(A, g0, A.planes + (uint64_t)rs * 3ull * A.plane_words, l, e, wmask, VP, VN, err, cols, dead);
+  else
+    verify_columns_general<HAS_N>(A, g0, A.codes + 2 * off + (uint64_t)dir * (uint64_t)l, l, e, wmask, VP, VN, err, cols, dead);
   uint32_t out = 0xFFFFFFFFu;
   if (!dead) {
     int best = err, end_off = l - 1;               // align.c:135-146

@@ -440,6 +440,18 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     va.result = s.result.as<uint32_t>();
     va.rs_map_count = s.rs_map_count.as<uint32_t>();
     va.cols_executed = &dc->cols_executed;
+    // bit planes of the batch's reads (one ballot per plane and 32 bases) for the plane form of the columns
+    const uint32_t plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
+    TRY(s.planes.reserve(n_rs * 3ull * plane_words * 4 + 16));
+    TRY(s.rs_has_n.reserve(n_rs + 16));
+    k_planes<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), (uint32_t)n_rs, plane_words,
+                                                             s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
+    ++s.n_launches;
+    va.refp0 = c->refp0.as<uint32_t>(); va.refp1 = c->refp1.as<uint32_t>();
+    va.planes = s.planes.as<uint32_t>();
+    va.plane_words = plane_words;
+    va.rs_has_n = s.rs_has_n.as<uint8_t>();
+    if (!c->verify_planes) va.refp0 = nullptr; // tests / experiments: the general form for every candidate
     const unsigned grid = (unsigned)((s.n_cand + 255) / 256);
     if (c->ref_has_n) k_verify<true><<<grid, 256, 0, s.stream>>>(va);
     else k_verify<false><<<grid, 256, 0, s.stream>>>(va);

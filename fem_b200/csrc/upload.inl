@@ -156,7 +156,7 @@ extern "C" int femgpu_upload_reference(femgpu_ctx *c, uint32_t n_rec, const char
   c->ref_total = total;
   c->ref_has_n = (any_n & 1) != 0;
   c->ref_canonical = (any_n & 2) == 0;
-  return 0;
+  return derive_ref_planes(c);
 }
 
 // The resident index, reference and record names of `src` copied device to device (NVLink peer copies
@@ -202,5 +202,19 @@ extern "C" int femgpu_clone_resident(femgpu_ctx *dst, const femgpu_ctx *src) {
   dst->ref_has_n = src->ref_has_n;
   dst->ref_canonical = src->ref_canonical;
   dst->have_rnames = src->have_rnames;
+  return derive_ref_planes(dst);
+}
+
+// Bit planes of the packed reference for k_verify's plane form (cheap to derive: one pass over ref2 on the device).
+static int derive_ref_planes(femgpu_ctx *c) {
+  const uint64_t n_words = (c->ref_total + 31) / 32;
+  TRY(c->refp0.reserve((n_words + 4) * 4));
+  TRY(c->refp1.reserve((n_words + 4) * 4));
+  cudaStream_t st = c->slot[0].stream;
+  CU(cudaMemsetAsync(c->refp0.p, 0, (n_words + 4) * 4, st));
+  CU(cudaMemsetAsync(c->refp1.p, 0, (n_words + 4) * 4, st));
+  if (n_words) k_ref_planes<<<(unsigned)((n_words + 255) / 256), 256, 0, st>>>(c->ref2.as<uint32_t>(), n_words, c->refp0.as<uint32_t>(), c->refp1.as<uint32_t>());
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(st));
   return 0;
 }

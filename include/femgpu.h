@@ -147,7 +147,8 @@ void femgpu_free_pinned(void *p);
  * choice on sparse indexes; 5 the near-pair path's register form (k_cand_reg) whatever the index density;
  * 6 the near-pair path without its register form), "small_shape" (k_cand_small: 0 automatic, 1 one seed per lane
  * when step x Q <= 32, 4 up to 128 seeds), "hash_slots", "pair_bits", "pair_values" (0 automatic),
- * "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
+ * "verify_planes" (1 default: k_verify computes candidates without ambiguous bases from bit planes; 0: the general
+ * form for all), "device_traceback" (1 default: k_trace fills femgpu_result.alns).  Returns FEMGPU_EINVAL for unknown keys. */
 int femgpu_set_option(femgpu_ctx *ctx, const char *key, int64_t value);
 
 /* ---- resident data --------------------------------------------------------------------------- */

@@ -212,6 +212,19 @@ def test_mappings_match_oracle(setup):
     assert n_checked > 0
 
 
+def test_verify_forms_agree(setup):
+    """k_verify's two forms of the Myers columns (src/align.c:102-277): bit planes (the default for candidates
+    without ambiguous bases) and the general five-row form; same mappings, same statistics."""
+    seqs = [r[1] for r in setup.reads]
+    want = setup.mapper.map_batch(seqs, setup.e, setup.a)
+    setup.mapper.set_option("verify_planes", 0)
+    try:
+        got = setup.mapper.map_batch(seqs, setup.e, setup.a)
+    finally:
+        setup.mapper.set_option("verify_planes", 1)
+    assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1]) and want[2] == got[2]
+
+
 def test_device_traceback_matches_oracle(setup):
     """k_trace: start, CIGAR and MD text of every mapping (src/align.c:279-544) against the oracle."""
     from fem_b200.api import ALN_HOST
