@@ -27,6 +27,10 @@ struct TraceArgs {
   int e;
   int ref_canonical;
   uint32_t *aln;               // out: 22 words per mapping (femgpu_alignment, 88 bytes)
+  // bit planes (k_ref_planes / k_planes, see k_verify.cuh); refp0 == nullptr: not available
+  const uint32_t *refp0, *refp1, *planes;
+  uint32_t plane_words;
+  const uint8_t *rs_has_n;
 };
 
 template <bool HAS_N>
@@ -98,19 +102,17 @@ __device__ uint32_t md_build_store(const DevRef &R, uint64_t gref, const uint8_t
   return (uint32_t)o;
 }
 
-// ---- reads and references without N: 16 bases per word ---------------------------------------------------
-// 16 reference bases from g on / 16 read bases from t on (tw: the read packed like ref2, one spare word)
-__device__ __forceinline__ uint32_t ref_word_at(const DevRef &R, uint64_t g) {
-  const uint32_t *p = R.ref2 + (g >> 4);
-  return __funnelshift_r(__ldg(p), __ldg(p + 1), 2u * ((uint32_t)g & 15u));
-}
-__device__ __forceinline__ uint32_t text_word_at(const uint32_t *tw, int t) {
-  return __funnelshift_r(tw[t >> 4], tw[(t >> 4) + 1], 2u * ((uint32_t)t & 15u));
+// ---- reads and references without N: bit planes, 32 bases per word --------------------------------------------
+// 32 bits of a plane from bit position g on
+__device__ __forceinline__ uint32_t plane_word_at(const uint32_t *p, uint64_t g) {
+  const uint32_t *w = p + (g >> 5);
+  return __funnelshift_r(__ldg(w), __ldg(w + 1), (uint32_t)g & 31u);
 }
 
-// md_build_store for an N-free reference and read: mismatches of a match run are found 16 bases at a time
-// (XOR of the packed words), so the cost follows the number of differences, not the read length
-__device__ uint32_t md_build_store_packed(const DevRef &R, uint64_t gref, const uint32_t *tw, const uint16_t *cig, int nc, uint32_t *dst) {
+// md_build_store for an N-free reference and read: the mismatches of a match run are the set bits of
+// (R0 ^ T0) | (R1 ^ T1), 32 bases at a time, so the cost follows the number of differences, not the read length
+__device__ uint32_t md_build_store_planes(const uint32_t *rp0, const uint32_t *rp1, uint64_t gref, const uint32_t *q0, const uint32_t *q1,
+                                          const uint16_t *cig, int nc, uint32_t *dst) {
   char md[48];
   int o = 0, tp = 0;
   uint32_t run = 0;
@@ -118,17 +120,17 @@ __device__ uint32_t md_build_store_packed(const DevRef &R, uint64_t gref, const 
     const uint32_t op = cig[ci] & 3u, len = cig[ci] >> 2;
     if (op == 0) {
       uint32_t pos = 0; // bases of this run already accounted for
-      for (uint32_t j0 = 0; j0 < len; j0 += 16) {
-        const uint32_t rw = ref_word_at(R, gref + j0), x = rw ^ text_word_at(tw, tp + (int)j0), n = min(16u, len - j0);
-        uint32_t mm = (x | (x >> 1)) & 0x55555555u;
-        if (n < 16u) mm &= (1u << (2u * n)) - 1u;
+      for (uint32_t j0 = 0; j0 < len; j0 += 32) {
+        const uint32_t r0 = plane_word_at(rp0, gref + j0), r1 = plane_word_at(rp1, gref + j0), n = min(32u, len - j0);
+        uint32_t mm = (r0 ^ plane_word_at(q0, (uint64_t)tp + j0)) | (r1 ^ plane_word_at(q1, (uint64_t)tp + j0));
+        if (n < 32u) mm &= (1u << n) - 1u;
         while (mm) {
-          const uint32_t b = (uint32_t)__ffs((int)mm) - 1u, j = j0 + (b >> 1);
+          const uint32_t b = (uint32_t)__ffs((int)mm) - 1u, j = j0 + b;
           mm &= mm - 1u;
           run += j - pos;
           pos = j + 1;
           if (run) { o = md_put_uint(md, o, run); run = 0; }
-          if (o < 48) md[o] = "ACGT"[(rw >> b) & 3u];
+          if (o < 48) md[o] = "ACGT"[((r0 >> b) & 1u) | (((r1 >> b) & 1u) << 1)];
           ++o;
         }
       }
@@ -142,7 +144,7 @@ __device__ uint32_t md_build_store_packed(const DevRef &R, uint64_t gref, const 
       if (o < 48) md[o] = '^';
       ++o;
       for (uint32_t j = 0; j < len; ++j) {
-        if (o < 48) md[o] = "ACGT"[ref_word_at(R, gref + j) & 3u];
+        if (o < 48) md[o] = "ACGT"[(plane_word_at(rp0, gref + j) & 1u) | ((plane_word_at(rp1, gref + j) & 1u) << 1)];
         ++o;
       }
       gref += len;
@@ -179,33 +181,18 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   const uint64_t g0 = A.ref.rec_base[rec.x >> 32] + (uint32_t)rec.x; // window[0]
   RefCursor<HAS_N> ref;
 
-  // the read 2 bits per base, as the reference is stored; packed = neither holds an N (every comparison
-  // below is then a word-wise XOR)
-  uint32_t tw[(LCAP + 15) / 16 + 1];
-  bool packed = !HAS_N;
-  if (!HAS_N) {
-    uint32_t any4 = 0;
-    for (int w = 0; w * 16 < l; ++w) {
-      uint32_t v = 0;
-      const int n = min(16, l - w * 16);
-      for (int j = 0; j < n; ++j) {
-        const uint32_t c = text[w * 16 + j];
-        any4 |= c;
-        v |= (c & 3u) << (2 * j);
-      }
-      tw[w] = v;
-    }
-    tw[(l + 15) / 16] = 0;
-    packed = (any4 & 4u) == 0;
-  }
+  // packed = neither the read nor the reference holds an N: every comparison below is a word-wise XOR of bit planes
+  // (k_planes wrote the read's for k_verify)
+  const bool packed = !HAS_N && A.refp0 && !A.rs_has_n[rs];
+  const uint32_t *q0 = A.planes + (uint64_t)rs * 3ull * A.plane_words, *q1 = q0 + A.plane_words;
 
   // :289-300 plain comparison at the reported end; no difference -> lM
   int diff = 0;
   if (packed) {
     const uint64_t gs = g0 + (uint64_t)start;
-    for (int t = 0; t < l; t += 16) {
-      uint32_t x = ref_word_at(A.ref, gs + (uint64_t)t) ^ text_word_at(tw, t);
-      if (l - t < 16) x &= (1u << (2 * (l - t))) - 1u;
+    for (int t = 0; t < l; t += 32) {
+      uint32_t x = (plane_word_at(A.refp0, gs + (uint64_t)t) ^ q0[t >> 5]) | (plane_word_at(A.refp1, gs + (uint64_t)t) ^ q1[t >> 5]);
+      if (l - t < 32) x &= (1u << (l - t)) - 1u;
       diff |= x != 0;
     }
   } else {
@@ -228,7 +215,33 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   // word (the band is 2e + 1 <= 15 bits wide; the walk below only looks at bit positions 0..15 and leaves
   // anything else to the host): half the local-memory traffic of two 32-bit histories
   uint32_t hist[LCAP];
-  {
+  if (packed) { // the columns from bit planes, as in k_verify's verify_columns_planes (32-bit words: no width mask)
+    const uint32_t band = (2u << (2 * e)) - 1u;
+    const uint32_t *r0p = A.refp0 + (g0 >> 5), *r1p = A.refp1 + (g0 >> 5);
+    const uint32_t s0 = (uint32_t)g0 & 31u;
+    uint32_t VP = 0, VN = 0;
+    uint32_t a0 = __funnelshift_r(__ldg(r0p), __ldg(r0p + 1), s0), a1 = __funnelshift_r(__ldg(r1p), __ldg(r1p + 1), s0);
+    for (int i0 = 0; i0 < l; i0 += 32) {
+      const int w = i0 >> 5;
+      const uint32_t b0 = __funnelshift_r(__ldg(r0p + w + 1), __ldg(r0p + w + 2), s0), b1 = __funnelshift_r(__ldg(r1p + w + 1), __ldg(r1p + w + 2), s0);
+      const uint32_t t0 = q0[w], t1 = q1[w];
+      const int n = min(32, l - i0);
+#pragma unroll 8
+      for (int ii = 0; ii < n; ++ii) {
+        uint32_t u0 = __funnelshift_r(a0, b0, ii), u1 = __funnelshift_r(a1, b1, ii);
+        if (t0 & (1u << ii)) u0 = ~u0;
+        if (t1 & (1u << ii)) u1 = ~u1;
+        uint32_t X = (~(u0 | u1) & band) | VN;
+        const uint32_t D0 = ((VP + (X & VP)) ^ VP) | X;
+        const uint32_t HP = VN | ~(VP | D0);
+        X = D0 >> 1;
+        VP = (VP & D0) | ~(X | HP);
+        VN = X & HP;
+        hist[i0 + ii] = (D0 & 0xFFFFu) | (HP << 16);
+      }
+      a0 = b0; a1 = b1;
+    }
+  } else {
     uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, p4 = 0, VP = 0, VN = 0;
     ref.seek(A.ref, g0);
     for (int i = 0; i < 2 * e; ++i) {
@@ -298,7 +311,7 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
   if (fail || n_ops - first + 1 > ALN_MAX_OPS) { aln_store(out, 0, ALN_HOST, cig); return; }
   int nc = 0;
   for (int i = n_ops; i >= first; --i) cig[nc++] = (uint16_t)(((uint32_t)cnt[i] << 2) | ops[i]);
-  const uint32_t md_len = packed ? md_build_store_packed(A.ref, g0 + (uint64_t)start, tw, cig, nc, out + 10)
+  const uint32_t md_len = packed ? md_build_store_planes(A.refp0, A.refp1, g0 + (uint64_t)start, q0, q1, cig, nc, out + 10)
                                  : md_build_store<HAS_N>(A.ref, g0 + (uint64_t)start, text, cig, nc, out + 10);
   aln_store(out, start, (uint32_t)nc, cig, md_len);
 }

@@ -34,23 +34,32 @@ struct VerifyArgs {
 
 // ---- bit planes ----------------------------------------------------------------------------------------
 // Reads: one warp per read-strand; 32 codes per round, a ballot per plane.
-__global__ void __launch_bounds__(256) k_planes(const uint8_t *codes, const uint64_t *read_off, uint32_t n_rs, uint32_t plane_words,
-                                                uint32_t *planes, uint8_t *rs_has_n) {
+__global__ void __launch_bounds__(256) k_planes(const uint8_t *codes, const uint64_t *read_off, const uint32_t *rs_cand_count, uint32_t n_rs,
+                                                uint32_t plane_words, uint32_t *planes, uint8_t *rs_has_n) {
   const uint32_t lane = lane_id();
   const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (rs >= n_rs) return;
+  if (rs >= n_rs || rs_cand_count[rs] == 0) return; // only read-strands with candidates are looked at again
   const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
   const uint64_t off = read_off[read];
   const uint32_t l = (uint32_t)(read_off[read + 1] - off);
   const uint8_t *text = codes + 2 * off + (uint64_t)dir * l;
   uint32_t *out = planes + rs * 3ull * plane_words;
   uint32_t any_n = 0;
-  for (uint32_t w = 0; w < plane_words; ++w) {
-    const uint32_t i = 32u * w + lane;
-    const uint32_t c = i < l ? text[i] : 0u;
-    const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1u), b1 = __ballot_sync(0xffffffffu, c & 2u), bn = __ballot_sync(0xffffffffu, c & 4u);
-    any_n |= bn;
-    if (lane == 0) { out[w] = b0; out[plane_words + w] = b1; out[2 * plane_words + w] = bn; }
+  for (uint32_t w0 = 0; w0 < plane_words; w0 += 8) { // eight rounds of loads in flight
+    uint32_t c[8];
+#pragma unroll
+    for (uint32_t u = 0; u < 8; ++u) {
+      const uint32_t i = 32u * (w0 + u) + lane;
+      c[u] = i < l ? text[i] : 0u;
+    }
+#pragma unroll
+    for (uint32_t u = 0; u < 8; ++u) {
+      if (w0 + u < plane_words) {
+        const uint32_t b0 = __ballot_sync(0xffffffffu, c[u] & 1u), b1 = __ballot_sync(0xffffffffu, c[u] & 2u), bn = __ballot_sync(0xffffffffu, c[u] & 4u);
+        any_n |= bn;
+        if (lane == 0) { out[w0 + u] = b0; out[plane_words + w0 + u] = b1; out[2 * plane_words + w0 + u] = bn; }
+      }
+    }
   }
   if (lane == 0) rs_has_n[rs] = any_n != 0;
 }

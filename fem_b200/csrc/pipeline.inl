@@ -444,7 +444,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     const uint32_t plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
     TRY(s.planes.reserve(n_rs * 3ull * plane_words * 4 + 16));
     TRY(s.rs_has_n.reserve(n_rs + 16));
-    k_planes<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), (uint32_t)n_rs, plane_words,
+    k_planes<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), s.rs_cand_count.as<uint32_t>(), (uint32_t)n_rs, plane_words,
                                                              s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
     ++s.n_launches;
     va.refp0 = c->refp0.as<uint32_t>(); va.refp1 = c->refp1.as<uint32_t>();
@@ -507,6 +507,10 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ta.e = pl.e;
     ta.ref_canonical = c->ref_canonical ? 1 : 0;
     ta.aln = s.aln.as<uint32_t>();
+    ta.refp0 = c->verify_planes ? c->refp0.as<uint32_t>() : nullptr; ta.refp1 = c->refp1.as<uint32_t>();
+    ta.planes = s.planes.as<uint32_t>();
+    ta.plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
+    ta.rs_has_n = s.rs_has_n.as<uint8_t>();
     const unsigned grid = (unsigned)((s.n_maps + 127) / 128);
     const int cap = s.l_max <= 128 ? 128 : s.l_max <= 256 ? 256 : 1024;
 #define LAUNCH_TRACE(N, L) k_trace<N, L><<<grid, 128, 0, s.stream>>>(ta)
