@@ -33,35 +33,42 @@ struct VerifyArgs {
 };
 
 // ---- bit planes ----------------------------------------------------------------------------------------
-// Reads: one warp per read-strand; 32 codes per round, a ballot per plane.
+// Reads: one thread per plane word (32 bases) of a read-strand with candidates.  The 32 code bytes are read as nine
+// aligned words, realigned by funnel shifts; bit b of four codes at once is gathered by a multiply.  rs_has_n is
+// zeroed before the launch.
+__device__ __forceinline__ uint32_t bits_of_bytes(uint32_t y) { // y: one bit per byte (at bit 0) -> those four bits
+  return (y * 0x01020408u) >> 24;
+}
 __global__ void __launch_bounds__(256) k_planes(const uint8_t *codes, const uint64_t *read_off, const uint32_t *rs_cand_count, uint32_t n_rs,
                                                 uint32_t plane_words, uint32_t *planes, uint8_t *rs_has_n) {
-  const uint32_t lane = lane_id();
-  const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t rs = t / plane_words;
+  const uint32_t w = (uint32_t)(t - rs * plane_words);
   if (rs >= n_rs || rs_cand_count[rs] == 0) return; // only read-strands with candidates are looked at again
   const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
   const uint64_t off = read_off[read];
   const uint32_t l = (uint32_t)(read_off[read + 1] - off);
-  const uint8_t *text = codes + 2 * off + (uint64_t)dir * l;
-  uint32_t *out = planes + rs * 3ull * plane_words;
-  uint32_t any_n = 0;
-  for (uint32_t w0 = 0; w0 < plane_words; w0 += 8) { // eight rounds of loads in flight
-    uint32_t c[8];
+  const uint8_t *p = codes + 2 * off + (uint64_t)dir * l + 32u * w;
+  const uint32_t *pa = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+  const uint32_t sh = 8u * (uint32_t)(reinterpret_cast<uintptr_t>(p) & 3u);
+  uint32_t b0 = 0, b1 = 0, bn = 0;
+  if (32u * w < l) { // the codes array is padded: the words past the read's end are readable, their bits masked below
+    uint32_t wd[9];
 #pragma unroll
-    for (uint32_t u = 0; u < 8; ++u) {
-      const uint32_t i = 32u * (w0 + u) + lane;
-      c[u] = i < l ? text[i] : 0u;
-    }
+    for (int k = 0; k < 9; ++k) wd[k] = __ldg(pa + k);
 #pragma unroll
-    for (uint32_t u = 0; u < 8; ++u) {
-      if (w0 + u < plane_words) {
-        const uint32_t b0 = __ballot_sync(0xffffffffu, c[u] & 1u), b1 = __ballot_sync(0xffffffffu, c[u] & 2u), bn = __ballot_sync(0xffffffffu, c[u] & 4u);
-        any_n |= bn;
-        if (lane == 0) { out[w0 + u] = b0; out[plane_words + w0 + u] = b1; out[2 * plane_words + w0 + u] = bn; }
-      }
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t x = __funnelshift_r(wd[k], wd[k + 1], sh);
+      b0 |= bits_of_bytes(x & 0x01010101u) << (4 * k);
+      b1 |= bits_of_bytes((x >> 1) & 0x01010101u) << (4 * k);
+      bn |= bits_of_bytes((x >> 2) & 0x01010101u) << (4 * k);
     }
+    const uint32_t n = l - 32u * w;
+    if (n < 32u) { const uint32_t m = (1u << n) - 1u; b0 &= m; b1 &= m; bn &= m; }
   }
-  if (lane == 0) rs_has_n[rs] = any_n != 0;
+  uint32_t *out = planes + rs * 3ull * plane_words + w;
+  out[0] = b0; out[plane_words] = b1; out[2 * plane_words] = bn;
+  if (bn) rs_has_n[rs] = 1;
 }
 
 // Reference: plane word j (bases 32 j .. 32 j + 31) from the two 2-bit words ref2[2 j], ref2[2 j + 1].

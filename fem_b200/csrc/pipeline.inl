@@ -128,7 +128,7 @@ static int slot_reserve(femgpu_ctx *c, Slot &s, const Plan &pl, uint32_t n_reads
   const uint64_t n_task = n_rs * pl.step;
   TRY(s.bases.reserve(n_bases + 16));
   TRY(s.read_off.reserve((n_reads + 1ull) * 8));
-  TRY(s.codes.reserve(2 * n_bases + 16));
+  TRY(s.codes.reserve(2 * n_bases + 64)); // k_planes reads nine aligned words from a plane word's first code on
   TRY(s.rs_status.reserve(n_rs + 16));
   TRY(s.read_flags.reserve(n_reads + 16));
   TRY(s.rs_before.reserve(n_rs * 4 + 16));
@@ -444,8 +444,9 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     const uint32_t plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
     TRY(s.planes.reserve(n_rs * 3ull * plane_words * 4 + 16));
     TRY(s.rs_has_n.reserve(n_rs + 16));
-    k_planes<<<(unsigned)((n_rs + 7) / 8), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), s.rs_cand_count.as<uint32_t>(), (uint32_t)n_rs, plane_words,
-                                                             s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
+    CU(cudaMemsetAsync(s.rs_has_n.p, 0, n_rs, s.stream));
+    k_planes<<<(unsigned)((n_rs * plane_words + 255) / 256), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), s.rs_cand_count.as<uint32_t>(),
+                                                                             (uint32_t)n_rs, plane_words, s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
     ++s.n_launches;
     va.refp0 = c->refp0.as<uint32_t>(); va.refp1 = c->refp1.as<uint32_t>();
     va.planes = s.planes.as<uint32_t>();
@@ -512,10 +513,10 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     ta.plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
     ta.rs_has_n = s.rs_has_n.as<uint8_t>();
     const unsigned grid = (unsigned)((s.n_maps + 127) / 128);
-    const int cap = s.l_max <= 128 ? 128 : s.l_max <= 256 ? 256 : 1024;
+    const int cap = s.l_max <= 128 ? 128 : s.l_max <= 160 ? 160 : s.l_max <= 256 ? 256 : 1024; // columns of per-thread history (local memory)
 #define LAUNCH_TRACE(N, L) k_trace<N, L><<<grid, 128, 0, s.stream>>>(ta)
-    if (c->ref_has_n) { if (cap == 128) LAUNCH_TRACE(true, 128); else if (cap == 256) LAUNCH_TRACE(true, 256); else LAUNCH_TRACE(true, 1024); }
-    else { if (cap == 128) LAUNCH_TRACE(false, 128); else if (cap == 256) LAUNCH_TRACE(false, 256); else LAUNCH_TRACE(false, 1024); }
+    if (c->ref_has_n) { if (cap == 128) LAUNCH_TRACE(true, 128); else if (cap == 160) LAUNCH_TRACE(true, 160); else if (cap == 256) LAUNCH_TRACE(true, 256); else LAUNCH_TRACE(true, 1024); }
+    else { if (cap == 128) LAUNCH_TRACE(false, 128); else if (cap == 160) LAUNCH_TRACE(false, 160); else if (cap == 256) LAUNCH_TRACE(false, 256); else LAUNCH_TRACE(false, 1024); }
 #undef LAUNCH_TRACE
     ++s.n_launches;
     CU(cudaGetLastError());
