@@ -277,11 +277,27 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
     if (n_ops >= ALN_MAX_OPS + 1) { fail = true; break; }                                          \
     ops[n_ops] = (uint8_t)run; cnt[n_ops++] = (uint16_t)run_n; run = (next); run_n = 1;            \
   } while (0)
+  // The walk is one long dependency chain, so its loads are kept off it: the history word of the next column is
+  // requested while this one is used, and (packed) "reference base == read base" comes from a 32-column match mask of
+  // the current diagonal rp - tp, rebuilt from the bit planes when the walk enters another 32-column block or an
+  // indel changes the diagonal.
+  uint32_t hcur = hist[tp], eqm = 0;
+  int eq_blk = -1, eq_delta = 0;
   while (tp >= 0 && (used != dist || tp == l - 1) && !fail) {
     const uint32_t sh = (uint32_t)bit & 31u; // the reference shifts by `bit`; out-of-range shifts are UB there
     if (bit < 0 || bit > 15) { fail = true; break; }
-    const uint32_t h = hist[tp] >> sh, d0 = h & 1u;
-    const bool same = rp >= 0 && ref_code_fetch<HAS_N>(A.ref, g0 + (uint64_t)rp) == text[tp];
+    const uint32_t hnext = tp > 0 ? hist[tp - 1] : 0u;
+    const uint32_t h = hcur >> sh, d0 = h & 1u;
+    const int tp_was = tp;
+    bool same;
+    if (packed && rp >= tp) {
+      if ((tp >> 5) != eq_blk || rp - tp != eq_delta) {
+        eq_blk = tp >> 5; eq_delta = rp - tp;
+        const uint64_t gb = g0 + (uint64_t)(32 * eq_blk + eq_delta);
+        eqm = ~((plane_word_at(A.refp0, gb) ^ q0[eq_blk]) | (plane_word_at(A.refp1, gb) ^ q1[eq_blk]));
+      }
+      same = (eqm >> (tp & 31)) & 1u;
+    } else same = rp >= 0 && ref_code_fetch<HAS_N>(A.ref, g0 + (uint64_t)rp) == text[tp];
     if (d0 && same) { // match
       --tp; --rp;
       if (run != OP_M) CLOSE_RUN(OP_M); else ++run_n;
@@ -296,6 +312,7 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
       --bit; --rp; ++used; --start;
       if (run != OP_D) CLOSE_RUN(OP_D); else ++run_n;
     }
+    if (tp != tp_was) hcur = hnext;
   }
   if (!fail && tp >= 0) { // :441-459 the rest of the read matches
     if (run != OP_M) { CLOSE_RUN(OP_M); run_n = tp + 1; }

@@ -65,7 +65,7 @@ launches)
 full)
   # the first pass over the whole 1 M-read batch (femgpu_map_batch): one launch of each hot kernel
   python bench.py $small > $out/${tag}_plain.log 2>&1 &&
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_seed|k_cand|k_verify|k_trace' -c 5 \
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_seed|k_cand_reg|k_verify|k_trace' -c 4 \
     -o $out/${tag}_full -f python bench.py $small > $out/${tag}_ncu_full.log 2>&1; echo "ncu full rc=$?" ;;
 probe)
   python bench.py $small > $out/${tag}_plain.log 2>&1 &&
