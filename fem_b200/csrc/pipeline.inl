@@ -405,6 +405,17 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   s.n_cand = hc.cand_count;
   s.stats.num_candidates_before_filter = hc.total_before;
   s.stats.num_candidates = hc.cand_count;
+  if (s.n_cand) {
+    // bit planes of the reads that have candidates (k_verify's and k_trace's plane forms); timed with this stage
+    const uint32_t plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
+    TRY(s.planes.reserve(n_rs * 3ull * plane_words * 4 + 16));
+    TRY(s.rs_has_n.reserve(n_rs + 16));
+    CU(cudaMemsetAsync(s.rs_has_n.p, 0, n_rs, s.stream));
+    k_planes<<<(unsigned)((n_rs * plane_words + 255) / 256), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), s.rs_cand_count.as<uint32_t>(),
+                                                                             (uint32_t)n_rs, plane_words, s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
+    ++s.n_launches;
+    CU(cudaGetLastError());
+  }
   cudaEventRecord(s.ev[2], s.stream);
   return 0;
 }
@@ -440,14 +451,7 @@ static int run_verify_and_compact(femgpu_ctx *c, Slot &s, const Plan &pl) {
     va.result = s.result.as<uint32_t>();
     va.rs_map_count = s.rs_map_count.as<uint32_t>();
     va.cols_executed = &dc->cols_executed;
-    // bit planes of the batch's reads (one ballot per plane and 32 bases) for the plane form of the columns
     const uint32_t plane_words = (uint32_t)((std::max(s.l_max, 1) + 31) / 32);
-    TRY(s.planes.reserve(n_rs * 3ull * plane_words * 4 + 16));
-    TRY(s.rs_has_n.reserve(n_rs + 16));
-    CU(cudaMemsetAsync(s.rs_has_n.p, 0, n_rs, s.stream));
-    k_planes<<<(unsigned)((n_rs * plane_words + 255) / 256), 256, 0, s.stream>>>(s.codes.as<uint8_t>(), s.read_off.as<uint64_t>(), s.rs_cand_count.as<uint32_t>(),
-                                                                             (uint32_t)n_rs, plane_words, s.planes.as<uint32_t>(), s.rs_has_n.as<uint8_t>());
-    ++s.n_launches;
     va.refp0 = c->refp0.as<uint32_t>(); va.refp1 = c->refp1.as<uint32_t>();
     va.planes = s.planes.as<uint32_t>();
     va.plane_words = plane_words;
