@@ -9,11 +9,11 @@
 //   loads   all occurrence words of the group are requested at once: runs 0..Q-2 side by side, LPR = 32/(Q-1)
 //           lanes per run and one aligned 32-byte sector per run and slot (when LPR is a multiple of 4), the
 //           last run 32 entries per slot; the loads of a whole group (~2.7 KB at cfg3) are in flight together;
-//   pass 1  every entry marks its 8-wide bucket in bitmap A (B: the bit was already set) and keeps the
-//           bitmap position, two to a register.  Entries the reference drops (position < seed offset,
+//   pass 1  every entry marks its 8-wide bucket in the bitmap (and the next bucket too when its own was taken: see
+//           preg_mark) and keeps the bitmap position, two to a register.  Entries the reference drops (position < seed offset,
 //           filter.c:89,106) are marked all the same: they can only add false flags, and the exact test
 //           follows below;
-//   flags   F = B | (A & (A << 1 | A >> 1)), as in k_cand_pair;
+//   flags   F = A & (A << 1 | A >> 1), in place;
 //   pass 2  one bit test per slot gives the lane's mask of flagged slots; only flagged entries (~30 of ~330
 //           per group at cfg3) are loaded again (cache hits), filtered exactly and written to the flagged list;
 //   exact   as in k_cand_pair: count in [x, x+e] among the flagged entries, rank sort, greedy merge.
@@ -29,29 +29,34 @@
 
 #define PREG_UB 3 // slots of the last run (32 entries each)
 
-// M bits per bitmap (power of two, 1024..32768)
+// M bits of the bitmap (power of two, 2048..32768: positions are kept in 16 bits)
 __host__ __device__ inline size_t cand_reg_smem_bytes_per_warp(uint32_t M) {
-  return (size_t)M / 8 * 2 + (PAIR_SC + 2 * PAIR_AC) * 8 + PAIR_FC * 8;
+  return (size_t)M / 8 + (PAIR_SC + 2 * PAIR_AC) * 8 + PAIR_FC * 8;
 }
 
-// Bitmap marks of NS slots at once: A's word at shared address bmA_s + 4 * (h >> 5); B's word, bmB_off bytes behind it,
-// when the bit was already set.  All NS first atomics are issued before the first result is looked at (a shared atomic
-// returns after ~30 cycles; one at a time, the kernel waited on the short scoreboard for a third of its cycles).
-// A slot without an entry ORs 0 into the word its filler value points at -- the fillers differ from lane to lane, so
-// these no-ops do not pile up on one address -- and so needs no predicate: ptxas turns a predicated shared atomic into
-// a divergence region (BSSY / BRA / ATOMS / BSYNC).
+// Bitmap marks of NS slots at once: the entry's 8-wide bucket h is bit h & 31 of the word at shared address
+// bm_s + 4 * (h >> 5).  An entry that finds its bit set already (two entries in one bucket) also marks the NEXT bucket:
+// "bucket and a neighbour both occupied" then flags the bucket of both, and no second bitmap is needed for buckets that
+// hold two entries -- which lets the one bitmap be twice as long in the same shared memory (half the false flags).
+// All NS first atomics are issued before the first result is looked at (a shared atomic returns after ~30 cycles; one
+// at a time, the kernel waited on the short scoreboard for a third of its cycles).  A slot without an entry ORs 0 into
+// the word its filler value points at -- the fillers differ from lane to lane, so these no-ops do not pile up on one
+// address -- and so needs no predicate: ptxas turns a predicated shared atomic into a divergence region.
 template <int NS>
-__device__ __forceinline__ void preg_mark(uint32_t bmA_s, uint32_t bmB_off, const uint32_t (&h)[NS], const uint32_t (&bit)[NS]) {
-  uint32_t addr[NS], old[NS];
+__device__ __forceinline__ void preg_mark(uint32_t bm_s, uint32_t mask, const uint32_t (&h)[NS], const uint32_t (&bit)[NS]) {
+  uint32_t old[NS];
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
-    asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 5;\n\tmad.lo.u32 %0, t, 4, %2;\n\t}" : "=r"(addr[i]) : "r"(h[i]), "r"(bmA_s));
-    asm volatile("atom.shared.or.b32 %0, [%1], %2;" : "=r"(old[i]) : "r"(addr[i]), "r"(bit[i]));
+    uint32_t addr;
+    asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 5;\n\tmad.lo.u32 %0, t, 4, %2;\n\t}" : "=r"(addr) : "r"(h[i]), "r"(bm_s));
+    asm volatile("atom.shared.or.b32 %0, [%1], %2;" : "=r"(old[i]) : "r"(addr), "r"(bit[i]));
   }
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
-    const uint32_t dup = old[i] & bit[i];
-    if (dup) asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr[i] + bmB_off), "r"(dup));
+    if (old[i] & bit[i]) {
+      const uint32_t h1 = (h[i] + 1u) & mask;
+      asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(bm_s + (h1 >> 5) * 4u), "r"(1u << (h1 & 31u)));
+    }
   }
 }
 
@@ -68,13 +73,12 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
     return;
   }
   unsigned char *base = reinterpret_cast<unsigned char *>(smem_reg) + (size_t)wib * cand_reg_smem_bytes_per_warp(M);
-  uint32_t *bmA = reinterpret_cast<uint32_t *>(base);          // occupied buckets
-  uint32_t *bmB = bmA + M / 32;                                // buckets with two entries, then the flag map F
-  const uint32_t bmA_s = (uint32_t)__cvta_generic_to_shared(bmA), bmB_off = M / 8;
-  uint64_t *surv = reinterpret_cast<uint64_t *>(bmB + M / 32);
+  uint32_t *bm = reinterpret_cast<uint32_t *>(base);           // occupied buckets, then (in place) the flagged buckets
+  const uint32_t bm_s = (uint32_t)__cvta_generic_to_shared(bm);
+  uint64_t *surv = reinterpret_cast<uint64_t *>(bm + M / 32);
   uint64_t *acc = surv + PAIR_SC, *acc2 = acc + PAIR_AC;
   uint64_t *fv = acc2 + PAIR_AC;                               // values of the flagged entries
-  const uint32_t a = (uint32_t)A.a, e32 = (uint32_t)A.e, mask = M - 1, wmask = M / 32 - 1;
+  const uint32_t a = (uint32_t)A.a, e32 = (uint32_t)A.e, mask = M - 1, nw = M / 32;
   const uint64_t e = (uint64_t)A.e;
   const uint32_t myrun = lane / LPR, sub = lane - myrun * LPR;
   const uint64_t filler = (uint64_t)(lane * 0x9E3779B1u); // lane-specific: the no-op atomics of empty slots spread over the words
@@ -136,8 +140,8 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
         if ((uint32_t)x >= rst) { mv = x - rst; has = true; break; } // filter.c:89,106
       }
     {
-      uint4 *z = reinterpret_cast<uint4 *>(bmA); // A and B are contiguous: 2 * M / 32 words
-      for (uint32_t t = lane; t < M / 64; t += 32) z[t] = make_uint4(0u, 0u, 0u, 0u);
+      uint4 *z = reinterpret_cast<uint4 *>(bm);
+      for (uint32_t t = lane; t < M / 128; t += 32) z[t] = make_uint4(0u, 0u, 0u, 0u);
     }
     if (!__any_sync(0xffffffffu, has)) continue; // nothing to merge the last run into
     mv = warp_max_u64(has ? mv : 0ull);
@@ -157,7 +161,7 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
           bit[i] = ((vm >> u) & 1u) << (h[i] & 31u);
           hs[u >> 1] |= h[i] << (16 * (u & 1));
         }
-        preg_mark<4>(bmA_s, bmB_off, h, bit);
+        preg_mark<4>(bm_s, mask, h, bit);
       }
     }
     // ---- pass 1, last run: entries up to the maximum of the others (ascending: the rest lies beyond) ----------
@@ -174,7 +178,7 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
         vm |= keep ? 1u << (UA + j) : 0u;
         hs[(UA + j) >> 1] |= h[j] << (16 * ((UA + j) & 1));
       }
-      preg_mark<UB>(bmA_s, bmB_off, h, bit);
+      preg_mark<UB>(bm_s, mask, h, bit);
     }
     // the next group's seeds have arrived by now: pull its occurrence runs into L2 (128-byte lines, one per lane of a
     // run, six for the last run) while this group is finished
@@ -185,16 +189,30 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
       if (lane < 2u * UB && 16u * lane < lf + 15u) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.occ + lb + 16u * lane));
     }
     __syncwarp();
-    // ---- flag map F = B | (A & (A rotated by one bucket either way)), four word pairs per lane and round --
-    for (uint32_t w0 = 4 * lane; w0 < M / 32; w0 += 128) {
-      const uint4 x = *reinterpret_cast<const uint4 *>(bmA + w0);
-      uint4 y = *reinterpret_cast<const uint4 *>(bmB + w0);
-      const uint32_t lft = bmA[(w0 - 1) & wmask], rgt = bmA[(w0 + 4) & wmask];
-      y.x |= x.x & (__funnelshift_l(lft, x.x, 1) | __funnelshift_r(x.x, x.y, 1));
-      y.y |= x.y & (__funnelshift_l(x.x, x.y, 1) | __funnelshift_r(x.y, x.z, 1));
-      y.z |= x.z & (__funnelshift_l(x.y, x.z, 1) | __funnelshift_r(x.z, x.w, 1));
-      y.w |= x.w & (__funnelshift_l(x.z, x.w, 1) | __funnelshift_r(x.w, rgt, 1));
-      *reinterpret_cast<uint4 *>(bmB + w0) = y;
+    // ---- flagged buckets F = A & (A rotated by one bucket either way), in place, four words per lane and round.  The
+    //      neighbour words come from the neighbour lanes' registers; the words across a round's edge are read before
+    //      they are overwritten (the last word of the previous round is carried, word 0 is kept for the wrap-around). ----
+    {
+      const uint32_t first = bm[0];
+      uint32_t carry = bm[nw - 1];
+      for (uint32_t r0 = 0; r0 < nw; r0 += 128) { // every lane takes every round (shuffles inside); nw >= 64
+        const uint32_t w0 = r0 + 4 * lane;
+        const bool in = w0 < nw;
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);
+        if (in) x = *reinterpret_cast<const uint4 *>(bm + w0);
+        uint32_t lft = __shfl_up_sync(0xffffffffu, x.w, 1), rgt = __shfl_down_sync(0xffffffffu, x.x, 1);
+        if (lane == 0) lft = carry;
+        if (w0 + 4 >= nw) rgt = first;
+        else if (lane == 31) rgt = bm[w0 + 4];
+        carry = __shfl_sync(0xffffffffu, x.w, 31);
+        uint4 y;
+        y.x = x.x & (__funnelshift_l(lft, x.x, 1) | __funnelshift_r(x.x, x.y, 1));
+        y.y = x.y & (__funnelshift_l(x.x, x.y, 1) | __funnelshift_r(x.y, x.z, 1));
+        y.z = x.z & (__funnelshift_l(x.y, x.z, 1) | __funnelshift_r(x.z, x.w, 1));
+        y.w = x.w & (__funnelshift_l(x.z, x.w, 1) | __funnelshift_r(x.w, rgt, 1));
+        __syncwarp(); // lane 31's read of the next round's first word is done before that round stores
+        if (in) *reinterpret_cast<uint4 *>(bm + w0) = y;
+      }
     }
     __syncwarp();
     // ---- pass 2: this lane's flagged slots ---------------------------------------------------------------
@@ -205,14 +223,14 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
 #pragma unroll
         for (int u = 4 * c; u < 4 * c + 4; ++u) {
           const uint32_t h = (hs[u >> 1] >> (16 * (u & 1))) & 0xFFFFu;
-          fm |= ((bmB[h >> 5] >> (h & 31u)) & 1u) << u;
+          fm |= ((bm[h >> 5] >> (h & 31u)) & 1u) << u;
         }
       }
     if (fl) {
 #pragma unroll
       for (int j = 0; j < (int)UB; ++j) {
         const uint32_t h = (hs[(UA + j) >> 1] >> (16 * ((UA + j) & 1))) & 0xFFFFu;
-        fm |= ((bmB[h >> 5] >> (h & 31u)) & 1u) << (UA + j);
+        fm |= ((bm[h >> 5] >> (h & 31u)) & 1u) << (UA + j);
       }
     }
     fm &= vm;

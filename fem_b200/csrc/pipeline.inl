@@ -14,6 +14,7 @@ struct Plan { // derived from params + the batch
   size_t hash_smem;
   uint32_t pair_M, pair_shift, pair_VC; // k_cand_pair: bitmap bits, 32 - log2(bits), values per warp
   size_t pair_smem, reg_smem;
+  uint32_t reg_M;     // k_cand_reg: bits of its one bitmap
   bool pair_reg; // k_cand_reg first (shape instantiated for this Q and runs expected to fit its slots)
   int first_path; // 0 sort, 1 hash, 2 pair, 3 small
   size_t small_smem;
@@ -103,7 +104,9 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
     const int lpr = pl->Q > 1 ? 32 / (pl->Q - 1) : 32;
     const bool shape = pl->Q == 5 || pl->Q == 7 || pl->Q == 9;
     const bool fits = mean + 3.3 * std::sqrt(mean) + 1.0 <= (double)(REG_UA * lpr - 3) && mean + 6.0 * std::sqrt(mean) <= 32.0 * PREG_UB;
-    pl->reg_smem = 4 * cand_reg_smem_bytes_per_warp(pl->pair_M);
+    // one bitmap of twice k_cand_pair's bits in the same shared memory (positions stay below 2^15)
+    pl->reg_M = std::max<uint32_t>(2048u, std::min<uint32_t>(32768u, 2u * pl->pair_M));
+    pl->reg_smem = 4 * cand_reg_smem_bytes_per_warp(pl->reg_M);
     pl->pair_reg = pl->a >= 1 && shape && c->cand_mode != 6 && (c->cand_mode == 5 || ((c->cand_mode == 0 || c->cand_mode == 3) && fits)) &&
                    pl->reg_smem <= c->smem_optin;
     if (c->cand_mode == 5 || c->cand_mode == 6) pl->first_path = pl->a >= 1 ? 2 : 1;
@@ -280,11 +283,11 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     else if (reg_first) {
       const unsigned grid = (unsigned)((n_rs + 3) / 4);
       static const int variant = getenv("FEM_REG_VARIANT") ? atoi(getenv("FEM_REG_VARIANT")) : 1; // experiments: resident blocks per SM (1: 8 blocks of 64 registers, measured best: 14.5 against 15.0 ms)
-      if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 8><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 7><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 9) k_cand_reg<9, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else if (pl.Q == 7) k_cand_reg<7, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
-      else k_cand_reg<5, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.pair_M);
+      if (pl.Q == 9 && variant == 1) k_cand_reg<9, REG_UA, 8><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.reg_M);
+      else if (pl.Q == 9 && variant == 2) k_cand_reg<9, REG_UA, 7><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.reg_M);
+      else if (pl.Q == 9) k_cand_reg<9, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.reg_M);
+      else if (pl.Q == 7) k_cand_reg<7, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.reg_M);
+      else k_cand_reg<5, REG_UA, 6><<<grid, 128, pl.reg_smem, s.stream>>>(ca, pl.reg_M);
       ++s.n_launches;
       // what it hands on goes to k_cand_pair without a trip to the host: the list's length is read on the device;
       // REG_CHAIN warps are launched, a longer list (seen below) gets a second launch for its tail
