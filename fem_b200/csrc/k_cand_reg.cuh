@@ -87,14 +87,13 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
   bool overflow = false;
   // seeds of the next group are fetched while the current one is processed
   uint32_t nb = 0, nfreq = 0, nst = 0;
-  const size_t so = (size_t)rs * A.step * Q + (lane < (uint32_t)Q ? lane : 0u);
-  const uint32_t *sp_b = A.seed_begin + so, *sp_f = A.seed_freq + so, *sp_s = A.seed_start + so; // this lane's seed of the next group
-  if (lane < (uint32_t)Q) { nb = *sp_b; nfreq = *sp_f; nst = *sp_s; }
+  size_t so = (size_t)rs * A.step * Q + (lane < (uint32_t)Q ? lane : 0u); // this lane's seed of the next group
+  if (lane < (uint32_t)Q) { nb = A.seed_begin[so]; nfreq = A.seed_freq[so]; nst = A.seed_start[so]; }
 
   for (int g = 0; g < A.step; ++g) {
     const uint32_t b = nb, f = nfreq, st = nst;
-    sp_b += Q; sp_f += Q; sp_s += Q;
-    if (g + 1 < A.step && lane < (uint32_t)Q) { nb = *sp_b; nfreq = *sp_f; nst = *sp_s; }
+    so += Q;
+    if (g + 1 < A.step && lane < (uint32_t)Q) { nb = A.seed_begin[so]; nfreq = A.seed_freq[so]; nst = A.seed_start[so]; }
     const uint32_t n_first = __reduce_add_sync(0xffffffffu, lane < R ? f : 0u); // all runs but the last
     if (n_first == 0) continue;                 // the last run alone contributes nothing (F5)
     // run registers of this lane: entry k0 + u * LPR of run myrun in slot u; with LPR a multiple of 4 every
@@ -189,29 +188,24 @@ __global__ void __launch_bounds__(128, MINB) k_cand_reg(CandArgs A, uint32_t M) 
     // ---- flagged buckets F = A & (A rotated by one bucket either way), in place, four words per lane and round.  The
     //      neighbour words come from the neighbour lanes' registers; the words across a round's edge are read before
     //      they are overwritten (the last word of the previous round is carried, word 0 is kept for the wrap-around). ----
-    if (nw >= 256) { // eight words per lane and round; every lane has words in every round
+    if (nw >= 128) { // four words per lane and round (eight: 2-way bank conflicts of the 16-byte accesses, 15.4 against 14.4 ms)
       const uint32_t first = bm[0];
       uint32_t carry = bm[nw - 1];
-      for (uint32_t r0 = 0; r0 < nw; r0 += 256) {
-        uint32_t *p = bm + r0 + 8 * lane;
-        const uint4 x = *reinterpret_cast<const uint4 *>(p), z = *reinterpret_cast<const uint4 *>(p + 4);
-        uint32_t lft = __shfl_up_sync(0xffffffffu, z.w, 1), rgt = __shfl_down_sync(0xffffffffu, x.x, 1);
-        const uint32_t next = r0 + 256 < nw ? bm[r0 + 256] : first; // the word after this round's last, still unchanged
+      for (uint32_t r0 = 0; r0 < nw; r0 += 128) {
+        uint32_t *p = bm + r0 + 4 * lane;
+        const uint4 x = *reinterpret_cast<const uint4 *>(p);
+        uint32_t lft = __shfl_up_sync(0xffffffffu, x.w, 1), rgt = __shfl_down_sync(0xffffffffu, x.x, 1);
+        const uint32_t next = r0 + 128 < nw ? bm[r0 + 128] : first; // the word after this round's last, still unchanged
         if (lane == 0) lft = carry;
         if (lane == 31) rgt = next;
-        carry = __shfl_sync(0xffffffffu, z.w, 31);
-        uint4 y, v;
+        carry = __shfl_sync(0xffffffffu, x.w, 31);
+        uint4 y;
         y.x = x.x & (__funnelshift_l(lft, x.x, 1) | __funnelshift_r(x.x, x.y, 1));
         y.y = x.y & (__funnelshift_l(x.x, x.y, 1) | __funnelshift_r(x.y, x.z, 1));
         y.z = x.z & (__funnelshift_l(x.y, x.z, 1) | __funnelshift_r(x.z, x.w, 1));
-        y.w = x.w & (__funnelshift_l(x.z, x.w, 1) | __funnelshift_r(x.w, z.x, 1));
-        v.x = z.x & (__funnelshift_l(x.w, z.x, 1) | __funnelshift_r(z.x, z.y, 1));
-        v.y = z.y & (__funnelshift_l(z.x, z.y, 1) | __funnelshift_r(z.y, z.z, 1));
-        v.z = z.z & (__funnelshift_l(z.y, z.z, 1) | __funnelshift_r(z.z, z.w, 1));
-        v.w = z.w & (__funnelshift_l(z.z, z.w, 1) | __funnelshift_r(z.w, rgt, 1));
+        y.w = x.w & (__funnelshift_l(x.z, x.w, 1) | __funnelshift_r(x.w, rgt, 1));
         __syncwarp(); // every read of this round (and of the next round's first word) is done before the stores
         *reinterpret_cast<uint4 *>(p) = y;
-        *reinterpret_cast<uint4 *>(p + 4) = v;
       }
     } else { // short bitmaps (tests): four words per lane, lanes past the end idle
       const uint32_t first = bm[0];
