@@ -212,6 +212,30 @@ def test_mappings_match_oracle(setup):
     assert n_checked > 0
 
 
+@pytest.mark.parametrize("mode", [0, 5, 6, 4, 2])
+def test_repeated_runs_are_bit_identical(setup, mode):
+    """compute-sanitizer is closed on this pool (profiles/r2v_sanitizer_closed_on_this_pool.txt), so a hazard between
+    lanes that hand data through shared memory (bitmaps, flagged lists, survivor lists, SAM images) has to show up as
+    what it causes: results that change from run to run.  Every candidate path maps the same batch six times; all
+    outputs -- candidates, mappings in emission order, alignments, statistics -- must be bit-identical (and the first
+    is checked against the oracle by the tests above)."""
+    seqs = [r[1] for r in setup.reads]
+    setup.mapper.set_option("cand_mode", mode)
+    try:
+        ref_c = setup.mapper.generate_group_seeding_candidates(seqs, setup.e, setup.a)
+        ref_m = setup.mapper.map_batch(seqs, setup.e, setup.a)
+        ref_a = setup.mapper.last_alignments.copy() if setup.mapper.last_alignments is not None else None
+        for _ in range(5):
+            c = setup.mapper.generate_group_seeding_candidates(seqs, setup.e, setup.a)
+            assert all(np.array_equal(x, y) for x, y in zip(ref_c, c))
+            m = setup.mapper.map_batch(seqs, setup.e, setup.a)
+            assert np.array_equal(ref_m[0], m[0]) and np.array_equal(ref_m[1], m[1]) and ref_m[2] == m[2]
+            if ref_a is not None:
+                assert np.array_equal(ref_a, setup.mapper.last_alignments)
+    finally:
+        setup.mapper.set_option("cand_mode", 0)
+
+
 def test_verify_forms_agree(setup):
     """k_verify's two forms of the Myers columns (src/align.c:102-277): bit planes (the default for candidates
     without ambiguous bases) and the general five-row form; same mappings, same statistics."""
