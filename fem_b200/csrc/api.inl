@@ -1,15 +1,19 @@
 // api.inl -- batch-level entry points (included by femgpu.cu)
 
-static int scan_batch(const femgpu_batch *b, uint64_t *n_bases, int *l_max) {
+static int scan_batch(const femgpu_batch *b, uint64_t *n_bases, int *l_max, uint32_t *n_too_long) {
   if (!b || (b->n_reads && (!b->bases || !b->offsets))) return set_error(FEMGPU_EINVAL, "null batch");
   uint64_t lm = 0;
+  *n_too_long = 0;
   for (uint32_t i = 0; i < b->n_reads; ++i) {
     if (b->offsets[i + 1] < b->offsets[i]) return set_error(FEMGPU_EINVAL, "read offsets must be non-decreasing");
-    lm = std::max(lm, b->offsets[i + 1] - b->offsets[i]);
+    const uint64_t l = b->offsets[i + 1] - b->offsets[i];
+    // a read beyond the seed kernel's shared-memory plan is left unmapped and counted as infeasible (k_seed marks
+    // it); the reference maps reads of any length, so the command line reports them like the too-short ones
+    if (l > (uint64_t)FEM_MAX_READ_LEN) ++*n_too_long;
+    else lm = std::max(lm, l);
   }
   if (b->n_reads && b->offsets[0] != 0) return set_error(FEMGPU_EINVAL, "offsets[0] must be 0");
   *n_bases = b->n_reads ? b->offsets[b->n_reads] : 0;
-  if (lm > (uint64_t)FEM_MAX_READ_LEN) return set_error(FEMGPU_EINVAL, "read of %llu bases exceeds the supported maximum %d", (unsigned long long)lm, FEM_MAX_READ_LEN);
   if (b->n_reads > 0x7FFFFFF0u / 2) return set_error(FEMGPU_EINVAL, "too many reads in one batch");
   *l_max = (int)lm;
   return 0;
@@ -20,8 +24,10 @@ static int stage_batch(femgpu_ctx *c, Slot &s, const femgpu_params *p, const fem
   CU(cudaSetDevice(c->device));
   uint64_t n_bases = 0;
   int l_max = 0;
-  TRY(scan_batch(b, &n_bases, &l_max));
-  TRY(make_plan(c, p, l_max, pl));
+  uint32_t n_too_long = 0;
+  TRY(scan_batch(b, &n_bases, &l_max, &n_too_long));
+  TRY(make_plan(c, p, l_max, pl, n_too_long != 0));
+  s.n_too_long = n_too_long;
   if (pl->seed_smem > c->smem_optin || pl->cand_smem > c->smem_optin || pl->hash_smem > c->smem_optin)
     return set_error(FEMGPU_EINVAL, "shared-memory plan too large (seed %zu, cand %zu bytes)", pl->seed_smem, pl->cand_smem);
   TRY(slot_reserve(c, s, *pl, b->n_reads, n_bases));
@@ -329,7 +335,7 @@ extern "C" int femgpu_rerun_resident(femgpu_ctx *c, float *ms_total, float ms_st
   if (s.busy) return set_error(FEMGPU_ESTATE, "slot busy");
   CU(cudaSetDevice(c->device));
   Plan pl;
-  TRY(make_plan(c, &s.params, s.l_max, &pl));
+  TRY(make_plan(c, &s.params, s.l_max, &pl, s.n_too_long != 0));
   cudaEventRecord(s.ev[0], s.stream);
   TRY(run_seed_and_candidates(c, s, pl));
   TRY(run_verify_and_compact(c, s, pl));

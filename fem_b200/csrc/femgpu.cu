@@ -145,7 +145,8 @@ struct Slot {
   femgpu_params params{};
   uint32_t n_reads = 0;
   uint64_t n_bases = 0;
-  int l_max = 0;
+  int l_max = 0;          // longest read within FEM_MAX_READ_LEN
+  uint32_t n_too_long = 0; // reads beyond it (left unmapped, counted as infeasible)
   uint64_t n_cand = 0, n_maps = 0;
   femgpu_stats stats{};
   float ms[6] = {0, 0, 0, 0, 0, 0};

@@ -68,6 +68,13 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
   const int l = (int)(A.read_off[read + 1] - off);
   const int n_s = l - k + 1;
   uint8_t *codes = A.codes + 2 * off + (uint64_t)dir * (uint64_t)l;
+  if (l > FEM_MAX_READ_LEN) { // beyond the shared-memory plan: left unmapped, counted as infeasible
+    if (lane == 0) {
+      A.rs_status[rs] = RS_INFEASIBLE; A.rs_before[rs] = 0; A.rs_max_f[rs] = 0; A.rs_sum_f[rs] = 0;
+      if (dir == 0) A.read_flags[read] = 0;
+    }
+    return;
+  }
 
   // ---- base codes (strand oriented), 2-bit packing, ambiguous-base count --------------------
   int amb = 0;

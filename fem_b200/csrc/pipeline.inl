@@ -22,7 +22,7 @@ struct Plan { // derived from params + the batch
   uint32_t small_inv_Q; // multiply-high reciprocal of Q for seed -> group
 };
 
-static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl) {
+static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl, bool over_long_reads = false) {
   if (!c->n_occ && !c->lut.p) return set_error(FEMGPU_ESTATE, "index not uploaded");
   if (!c->n_rec) return set_error(FEMGPU_ESTATE, "reference not uploaded");
   pl->k = p->k > 0 ? p->k : c->idx_k;
@@ -56,7 +56,8 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl)
   // group) it is bound by the shared-memory pipe (ncu: short-scoreboard and MIO-throttle stalls) at 6.2 against
   // 3.7 ms, so the one-read-strand form stays there.
   pl->seed_R = 0;
-  if ((c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
+  // over-long reads are marked by k_seed alone
+  if (!over_long_reads && (c->seed_dp_mode == 0 || c->seed_dp_mode == 3) && pl->lane_dp && pl->w_max <= 254 && pl->step <= 32 && pl->ns_max < 65536) {
     pl->seed_words_per_rs = seed_multi_words_per_rs(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step);
     // read-strands per warp: as many as fill the DP's lanes, but at most four -- smaller regions mean more warps
     // beside the L1 half of the SM (cfg2 per 1 M reads: 8 per warp 1.78 ms, 6: 1.66, 4: 1.65, 2: 2.03)

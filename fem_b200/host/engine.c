@@ -427,6 +427,14 @@ static void batch_sam_room(batch *b, size_t text_bytes, size_t n_off) {
   }
 }
 
+/* grow-only array of a batch; 0 on success (the old block stays valid on failure) */
+static int batch_grow(void **p, size_t bytes) {
+  void *q = realloc(*p, bytes ? bytes : 1);
+  if (!q) return -1;
+  *p = q;
+  return 0;
+}
+
 /* marks a batch complete for the writer */
 static void batch_finished(run_state *r, batch *b) {
   b->t_trace[3] = femhost_now();
@@ -468,15 +476,21 @@ static void *gpu_main(void *arg) {
       if (rc) { run_fail(r, femgpu_last_error()); ok = 0; }
       else {
         const uint64_t n_maps = res.first[n];
-        if ((size_t)n + 1 > b->cap_first) { b->cap_first = (size_t)n + 1; b->first = (uint64_t *)realloc(b->first, b->cap_first * 8); }
-        if (n_maps > b->cap_maps) { b->cap_maps = n_maps + n_maps / 4 + 1024; b->maps = (femgpu_mapping *)realloc(b->maps, b->cap_maps * sizeof(femgpu_mapping)); }
+        int oom = 0;
+        if ((size_t)n + 1 > b->cap_first) { if (batch_grow((void **)&b->first, ((size_t)n + 1) * 8)) oom = 1; else b->cap_first = (size_t)n + 1; }
+        if (!oom && n_maps > b->cap_maps) {
+          const size_t want = n_maps + n_maps / 4 + 1024;
+          if (batch_grow((void **)&b->maps, want * sizeof(femgpu_mapping))) oom = 1; else b->cap_maps = want;
+        }
+        if (!oom && res.alns && n_maps > b->cap_alns) {
+          const size_t want = n_maps + n_maps / 4 + 1024;
+          if (batch_grow((void **)&b->alns, want * sizeof(femgpu_alignment))) oom = 1; else b->cap_alns = want;
+        }
+        if (oom) { run_fail(r, "out of memory for a batch's results"); batch_finished(r, b); continue; }
         memcpy(b->first, res.first, ((size_t)n + 1) * 8);
         memcpy(b->maps, res.maps, n_maps * sizeof(femgpu_mapping));
         b->has_alns = res.alns != NULL;
-        if (res.alns) {
-          if (n_maps > b->cap_alns) { b->cap_alns = n_maps + n_maps / 4 + 1024; b->alns = (femgpu_alignment *)realloc(b->alns, b->cap_alns * sizeof(femgpu_alignment)); }
-          memcpy(b->alns, res.alns, n_maps * sizeof(femgpu_alignment));
-        }
+        if (res.alns) memcpy(b->alns, res.alns, n_maps * sizeof(femgpu_alignment));
         b->has_sam = res.sam_off != NULL;
         if (b->has_sam) {
           const uint64_t nb = res.sam_off[n];
@@ -501,9 +515,13 @@ static void *gpu_main(void *arg) {
     /* hand the batch to the SAM workers, CHUNK_READS reads at a time */
     const uint32_t n_chunks = (n + CHUNK_READS - 1) / CHUNK_READS;
     if (n_chunks > b->cap_chunks) {
-      b->text = (femhost_str *)realloc(b->text, n_chunks * sizeof(femhost_str));
+      if (batch_grow((void **)&b->text, n_chunks * sizeof(femhost_str)) || batch_grow((void **)&b->items, n_chunks * sizeof(work_item))) {
+        run_fail(r, "out of memory for a batch's SAM chunks");
+        b->n_chunks = 0;
+        batch_finished(r, b);
+        continue;
+      }
       memset(b->text + b->cap_chunks, 0, (n_chunks - b->cap_chunks) * sizeof(femhost_str));
-      b->items = (work_item *)realloc(b->items, n_chunks * sizeof(work_item));
       b->cap_chunks = n_chunks;
     }
     b->n_chunks = n_chunks;

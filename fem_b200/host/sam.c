@@ -6,6 +6,7 @@
  * bam1_t is built: the line is written straight into a text buffer, byte for byte what
  * sam_write1 would print for the record the reference fills in.
  */
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -185,6 +186,7 @@ int femhost_alignment(const char *window, const char *text, int l, int e, int ed
  * (extern/htslib/hts.c:73-94): IUPAC letters (either case) as upper case, '=' as '=', digits
  * 0..3 as ACGT, anything else 'N' */
 static char g_seq_out[256];
+static pthread_once_t g_seq_out_once = PTHREAD_ONCE_INIT;
 static void init_seq_out(void) {
   static const char iupac[] = "=ACMGRSVTWYHKDBN";
   char t[256];
@@ -208,7 +210,7 @@ static void make_rc(const char *seq, int l, char *rc) {
 int femhost_sam_read(const femhost_records *ref, const char *name, const char *seq, const char *qual, int l, int e,
                      femgpu_mapping *maps, femgpu_alignment *alns, size_t n, femhost_str *out) {
   if (n == 0) return 0; /* src/map.c:50: unmapped reads print nothing */
-  if (g_seq_out['A'] != 'A') init_seq_out();
+  pthread_once(&g_seq_out_once, init_seq_out); /* several SAM workers call this at once */
   femgpu_sort_mappings_aln(maps, alns, n); /* src/align.c:57; the device alignments follow their mappings */
   const size_t name_l = strlen(name);
   char rc[l + 1], md[4 * l + 64];

@@ -2,8 +2,8 @@
 one-read batches, ragged read lengths from k up to the supported maximum (reads too short to seed are
 the reference's crash cases: they must come back unmapped and counted), reads of only N, duplicated
 reads, homopolymer / tandem-repeat reads with thousands of locations (global-scratch candidate path,
-SAM records beyond the device formatter's limits), and a read longer than the maximum (an error, not a
-crash).  Bit-exact: integer work, no tolerance."""
+SAM records beyond the device formatter's limits), and a read longer than the maximum (left unmapped and counted,
+not an error).  Bit-exact: integer work, no tolerance."""
 import numpy as np
 import pytest
 
@@ -152,13 +152,20 @@ def test_low_complexity_reads(world, tmp_path):
     assert stats[4] > 5000
 
 
-def test_read_longer_than_the_maximum_is_an_error(world):
+def test_read_longer_than_the_maximum_is_left_unmapped(world):
+    """one read beyond the seed kernel's shared-memory plan (1024 bases) used to abort the whole batch (and
+    with it the `FEM map` run); it is now treated like the reads the reference cannot process -- left unmapped, counted
+    in num_infeasible_reads -- while the other reads of the batch map as if it were not there."""
     from fem_b200.api import FemGpuError
     long_read = bytes(np.random.default_rng(3).choice(np.frombuffer(b"ACGT", dtype=np.uint8), 1025))
-    with pytest.raises(FemGpuError):
-        world.mapper.map_batch([long_read], E, A)
     reads = synth.simulate_reads(9, world.records[:2], 10, 100, E)
-    assert world.mapper.map_batch([r[1] for r in reads], E, A)[2][0] == 10  # still usable
+    seqs = [r[1] for r in reads]
+    want_first, want_maps, want_stats = world.mapper.map_batch(seqs, E, A)
+    first, maps, stats = world.mapper.map_batch(seqs[:4] + [long_read] + seqs[4:] + [long_read], E, A)
+    assert stats[0] == 12 and stats[5] == want_stats[5] + 2 and stats[1:5] == want_stats[1:5]
+    assert first[5] == first[4] and first[12] == first[11]  # no mappings for the long reads
+    assert np.array_equal(maps, want_maps)
+    assert world.mapper.map_batch(seqs, E, A)[2] == want_stats  # and the plan goes back to normal
     with pytest.raises(FemGpuError):
         world.mapper.map_batch([reads[0][1]], 8, A)  # src/FEM_map.c:30 "Wrong error threshold."
     with pytest.raises(FemGpuError):
