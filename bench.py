@@ -552,7 +552,9 @@ def run_ours(args):
                                    "sampled during the probe = %.0f Gop/s; the LOP3 reading is used when it lies within 0.90..1.02 of nominal, else nominal"
                                    % (giops[0], giops[1], giops[2], sms, pc.get("sm_mhz") or 0, nominal),
                     "ncu_pipe_alu_pct": ncu_alu, "ncu_source": cap.get("k_verify_source") if cap else None,
-                    "columns_executed": cols, "candidates": n_cand, "ops_counted": "24 per executed column + 12e per candidate (src/align.c:118-133, SURVEY.md 8(d))"}
+                    "columns_executed": cols, "candidates": n_cand, "ops_counted": "24 per executed column + 12e per candidate (src/align.c:118-133, SURVEY.md 8(d))",
+                    "note": "the plane form executes 20 SASS instructions per column (profiles/r2_sass_k_verify_column.txt): LOP3 fuses pairs of the 24 counted "
+                            "operations, so the op-count fraction can pass the pipe's INSTRUCTION rate; ncu_pipe_alu_pct is the utilisation of the pipe itself"}
 
     line = {"metric": "reads/sec (all locations)", "value": value, "value_scope": "resident: reads already in HBM, every kernel from seeding to the SAM text",
             "unit": "reads/s", "n_gpus": world, "steps": args.steps,
