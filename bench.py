@@ -71,6 +71,7 @@ def parse_args():
     ap.add_argument("--data-dir", default=os.environ.get("FEM_BENCH_DIR", "/tmp/fem_bench"))
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="reads of the workload the CPU baseline maps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0, help="-t of the reference's CPU runs (default: all host cores; BASELINE.json configs[0] names -t 8)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (default: --steps)")
     ap.add_argument("--e2e-threads", type=int, default=0, help="host threads of the end-to-end leg (default: cores/ranks - 3)")
     ap.add_argument("--e2e-batch", type=int, default=0, help="reads per GPU batch of the end-to-end leg (default: the engine's)")
@@ -283,7 +284,7 @@ def run_reference(args):
         return 0
     fa, idx, fq = ensure_data(args, 0, 1, lambda: None)
     sample = head_fastq(fq, fq + ".cpu%d" % args.cpu_sample, args.cpu_sample)
-    cores = cpu_cores()
+    cores = args.cpu_threads or cpu_cores()
     out = "/dev/shm/fem_bench_ref.sam" if os.path.isdir("/dev/shm") else os.path.join(args.data_dir, "ref.sam")
     times = []
     for i in range(args.warmup + args.steps):
@@ -570,17 +571,18 @@ def run_ours(args):
     # ---- CPU baseline beside it (rank 0, N=1 only) ---------------------------------------------------
     if world == 1 and not args.no_cpu_baseline and os.access(REF_HDR, os.X_OK):
         sample = head_fastq(fq, fq + ".cpu%d" % args.cpu_sample, args.cpu_sample)
-        secs, n = time_reference(fa, idx, sample, w["e"], w["a"], cores, out + ".ref")
+        ref_threads = args.cpu_threads or cores
+        secs, n = time_reference(fa, idx, sample, w["e"], w["a"], ref_threads, out + ".ref")
         # untimed: the same sample through this repository's path, compared record for record
         hm.map_file(sample, out + ".ours", w["e"], w["a"], threads=threads)
         ref_g, our_g = sam_groups(out + ".ref"), sam_groups(out + ".ours")
         line["parity_vs_reference"] = {"reads": n, "sam_records": sum(len(v) for k, v in ref_g.items() if k is not None),
                                        "identical": ref_g == our_g,
-                                       "how": "header + per-read record groups (content and order) of oracle/_ref/FEM_ref_hdr -t %d vs femhost_map_file on the same reads" % cores}
+                                       "how": "header + per-read record groups (content and order) of oracle/_ref/FEM_ref_hdr -t %d vs femhost_map_file on the same reads" % ref_threads}
         os.remove(out + ".ref")
         os.remove(out + ".ours")
-        line["cpu_baseline"] = {"value": n / secs, "unit": "reads/s", "cores": cores, "kind": "reference",
-                                "sample": "first %d reads of the workload, oracle/_ref/FEM_ref_hdr map -t %d, its own Time: window" % (n, cores)}
+        line["cpu_baseline"] = {"value": n / secs, "unit": "reads/s", "cores": ref_threads, "kind": "reference",
+                                "sample": "first %d reads of the workload, oracle/_ref/FEM_ref_hdr map -t %d, its own Time: window" % (n, ref_threads)}
     elif world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = {"value": None, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": "oracle/_ref/FEM_ref_hdr not built"}
     hm.close()
