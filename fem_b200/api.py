@@ -102,6 +102,7 @@ EXPORTS = {
     "femgpu_measure_int32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double * 3)]),
     "femgpu_last_work": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64 * 4)]),
     "femgpu_rerun_resident": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float * 6)]),
+    "femgpu_lookup_table_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None
@@ -126,6 +127,17 @@ def load_library():
 def _check(rc):
     if rc != 0:
         raise FemGpuError("femgpu error %d: %s" % (rc, load_library().femgpu_last_error().decode(errors="replace")))
+
+
+NOALLOC_MAX_BUCKETS = 1 << 24  # FEMGPU_NOALLOC_MAX_BUCKETS
+
+
+def lookup_table_noalloc(device, counts_ptr, n_buckets, lut_ptr, stream=0):
+    """femgpu_lookup_table_noalloc: lut[0] = 0, lut[h + 1] = counts[0] + ... + counts[h], from DEVICE pointers,
+    queued on `stream` (a cudaStream_t as an integer), with its scratch in a static device array of the library
+    -- no allocation of any kind.  No counterpart in the reference (see include/femgpu.h)."""
+    _check(load_library().femgpu_lookup_table_noalloc(int(device), C.c_void_p(counts_ptr), int(n_buckets),
+                                                      C.c_void_p(lut_ptr), C.c_void_p(stream)))
 
 
 def sort_mappings_aln(maps: np.ndarray, alns: np.ndarray):

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -335,4 +336,5 @@ static int derive_ref_planes(femgpu_ctx *c);
 #include "upload.inl"
 #include "pipeline.inl"
 #include "index_build.inl"
+#include "noalloc.inl"
 #include "api.inl"

@@ -225,6 +225,26 @@ void femgpu_sort_mappings(femgpu_mapping *maps, size_t n);
 /* the same, carrying the parallel array of device alignments along (alns may be NULL) */
 void femgpu_sort_mappings_aln(femgpu_mapping *maps, femgpu_alignment *alns, size_t n);
 
+/* ---- an entry point that allocates nothing ---------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The lookup table of the index (the prefix sums of src/index.c:57-98 that femgpu_build_index computes
+ * with a cudaMalloc'ed buffer of tile sums) from per-bucket counts: d_lut[0] = 0,
+ * d_lut[h + 1] = d_counts[0] + ... + d_counts[h] (uint32 sums; the total must fit, as it does for any
+ * index the reference can write).  d_counts (n_buckets entries) and d_lut (n_buckets + 1 entries) are
+ * DEVICE pointers of the caller on `device`; stream is a cudaStream_t (NULL: the default stream).
+ * The three kernels are queued on that stream and the call returns without waiting for them.
+ * The tile sums live in a static device array inside the library (32 KB per GPU, held until exit),
+ * which bounds the size: 1 <= n_buckets <= FEMGPU_NOALLOC_MAX_BUCKETS (4^12, the reference's default
+ * window), FEMGPU_EINVAL with a message beyond.  The call makes no cudaMalloc, cudaFree or other
+ * allocating call; the first call per device looks the array's address up (cudaGetSymbolAddress),
+ * so make one call before a graph capture starts.  Every call on a device shares the array: calls
+ * that overlap on the GPU (two streams, two threads) race -- order them.  Nothing in it has to
+ * start at zero (each call overwrites the part it reads). */
+#define FEMGPU_NOALLOC_MAX_BUCKETS 16777216ull
+int femgpu_lookup_table_noalloc(int device, const uint32_t *d_counts, uint64_t n_buckets, uint32_t *d_lut,
+                                void *stream);
+
 /* ---- measurement hooks ------------------------------------------------------------------------ */
 /* Device time (CUDA events on the context's stream) of the kernels of the last finished batch, in
  * milliseconds: [0] pack+seed, [1] candidates, [2] verify, [3] compaction, [4] traceback,
