@@ -553,6 +553,7 @@ typedef struct {
   run_state *r;
   fifo *q;                  /* q_work: SAM text of chunks; q_write: copies into the output file */
   double busy, busy_write;
+  double t_populate, t_copy, t_unmap; /* FEM_TRACE: parts of busy_write */
 } worker_arg;
 
 static int write_all(int fd, const char *p, size_t n, int positional, uint64_t off) {
@@ -582,17 +583,25 @@ static void *worker_main(void *arg) {
 #define MADV_POPULATE_WRITE 23
 #endif
         const size_t wl = it->ext ? it->ext_len : out->l;
+        const double tp0 = r->trace ? femhost_now() : 0;
         if (r->out_populate && wl) { /* all pages of the chunk in one call instead of one fault each */
           const uintptr_t pg = (uintptr_t)sysconf(_SC_PAGESIZE), p0 = (uintptr_t)dst & ~(pg - 1);
           madvise((void *)p0, (size_t)((uintptr_t)dst + wl - p0), MADV_POPULATE_WRITE);
         }
+        const double tp1 = r->trace ? femhost_now() : 0;
         memcpy(dst, it->ext ? it->ext : out->s, it->ext ? it->ext_len : out->l);
+        if (r->trace) { wa->t_populate += tp1 - tp0; wa->t_copy += femhost_now() - tp1; }
       }
       else if (write_all(r->out_fd, it->ext ? it->ext : out->s, it->ext ? it->ext_len : out->l, 1, it->file_off)) run_fail(r, "short write to the SAM file");
       pthread_mutex_lock(&r->mu);
       const int left = --b->writes_left;
       pthread_mutex_unlock(&r->mu);
-      if (left == 0 && b->map_base) { munmap(b->map_base, b->map_len); b->map_base = NULL; }
+      if (left == 0 && b->map_base) {
+        const double tu0 = r->trace ? femhost_now() : 0;
+        munmap(b->map_base, b->map_len);
+        b->map_base = NULL;
+        if (r->trace) wa->t_unmap += femhost_now() - tu0;
+      }
       wa->busy_write += femhost_now() - t0;
       if (left == 0 && r->trace)
         fprintf(stderr, "[trace] batch %" PRIu64 " (%u reads): parsed %.1f, gpu %.1f-%.1f, text %.1f, offsets %.1f, written %.1f ms\n", b->seq,
@@ -906,6 +915,11 @@ static int map_file_run(femhost_mapper *m, const femhost_map_options *opt, const
   if (r.out_fd >= 0 && close(r.out_fd) != 0) run_fail(&r, "closing the SAM file failed");
   pthread_cond_destroy(&r.writes_done);
   r.tm.wall = femhost_now() - t_start;
+  if (r.trace) {
+    double tp = 0, tc = 0, tu = 0;
+    for (int i = 0; i < n_workers; ++i) { tp += wa[i].t_populate; tc += wa[i].t_copy; tu += wa[i].t_unmap; }
+    fprintf(stderr, "[trace] copiers: populate %.3f s, copy %.3f s, unmap %.3f s of write %.3f s\n", tp, tc, tu, r.tm.write);
+  }
   if (r.trace) fprintf(stderr, "[trace] entry to thread start %.1f ms, threads %.1f ms\n", 1e3 * (t_start - r.t_enter), 1e3 * r.tm.wall);
   if (r.rd) femhost_reader_close(r.rd);
   if (r.fd >= 0) close(r.fd);
