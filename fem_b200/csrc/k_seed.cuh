@@ -26,6 +26,7 @@ struct SeedArgs {
   int k, step, e, a, Q, s;
   int n_words_max, ns_max, w_max; // shared-memory plan for the longest read of the batch
   int lane_dp;
+  uint32_t smem_words;        // seed_smem_words_per_warp of this plan
   uint8_t *codes;             // out: 2 * total_bases; strand d of read i at 2*off[i] + d*len
   uint8_t *read_flags;        // out: per read, bit 0 = a character outside "ACGTN" (k_trace leaves it to the host)
   uint8_t *rs_status;         // out: per read-strand
@@ -47,16 +48,15 @@ __host__ __device__ inline size_t seed_smem_words_per_warp(int n_words_max, int 
          ((size_t)step * Q + 1) / 2;
 }
 
-__global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
+__global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   extern __shared__ uint32_t smem_seed[];
   const uint32_t lane = lane_id();
   const uint32_t warp_in_block = threadIdx.x >> 5;
   const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp_in_block;
   if (rs >= 2ull * A.n_reads) return;
   const int k = A.k, step = A.step, Q = A.Q, s = A.s, w_max = A.w_max;
-  const size_t groups = A.lane_dp ? (size_t)step : 1;
-  const size_t per_warp = seed_smem_words_per_warp(A.n_words_max, A.ns_max, w_max, Q, step, A.lane_dp);
-  uint32_t *pw = smem_seed + warp_in_block * per_warp;      // 2-bit packed read, big-endian in word
+  const uint32_t groups = A.lane_dp ? (uint32_t)step : 1u;
+  uint32_t *pw = smem_seed + warp_in_block * A.smem_words;  // 2-bit packed read, big-endian in word
   uint32_t *sm_freq = pw + A.n_words_max;
   uint32_t *sm_begin = sm_freq + A.ns_max;
   uint32_t *m_rows = sm_begin + A.ns_max;                   // [groups][w_max + 1], columns 0..W
@@ -77,27 +77,37 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
   }
 
   // ---- base codes (strand oriented), 2-bit packing, ambiguous-base count --------------------
-  int amb = 0;
+  // Four consecutive bases per lane and trip (128 bases per trip: a 150 bp read takes two).  A byte ch is a letter of
+  // "ACGT" in either case iff x = ch ^ 0x40 without its case bit is < 32 and bit x of ACGT_MASK is set (A 1, C 3, G 7,
+  // T 20); its code (src/utils.h:72) is then ((ch >> 1) ^ (ch >> 2)) & 3 -- A 0, C 1, G 2, T 3 -- and 4 otherwise.
+  constexpr uint32_t ACGT_MASK = (1u << 1) | (1u << 3) | (1u << 7) | (1u << 20), ACGTN_MASK = ACGT_MASK | (1u << 14);
+  uint32_t amb_lane = 0;
   bool noncanon = false;
   const int n_words = (l + 15) / 16 + 1;
-  for (int base = 0; base < n_words * 16; base += 32) {
-    const int i = base + (int)lane;
-    uint32_t c = 0, valid = i < l;
-    if (valid) {
-      const unsigned char ch = (unsigned char)(dir ? A.bases[off + (uint64_t)(l - 1 - i)] : A.bases[off + (uint64_t)i]);
-      c = fem_base_code(ch);
-      noncanon |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'N');
-      if (dir && c < 4) c = 3u - c; // 3 ^ code; ambiguous stays ambiguous (-> 'N')
-      codes[i] = (uint8_t)c;
+  const char *rb = A.bases + off;
+  for (int base = 0; base < n_words * 16; base += 128) {
+    const int i0 = base + 4 * (int)lane;
+    uint32_t v = 0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int i = i0 + t;
+      if (i < l) {
+        const uint32_t ch = (unsigned char)(dir ? rb[l - 1 - i] : rb[i]);
+        const uint32_t x = ch ^ 0x40u;
+        const bool acgt = (x & 0xDFu) < 32u && ((ACGT_MASK >> (x & 31u)) & 1u);
+        noncanon |= !(x < 32u && ((ACGTN_MASK >> (x & 31u)) & 1u)); // anything but upper-case "ACGTN"
+        uint32_t c = ((ch >> 1) ^ (ch >> 2)) & 3u;
+        if (dir) c ^= 3u;                        // complement; ambiguous stays ambiguous (-> 'N')
+        if (!acgt) { c = 4u; amb_lane += i >= k; } // only incoming bases count, utils.h:113
+        codes[i] = (uint8_t)c;
+        v |= (c & 3u) << (30 - 8 * (int)(lane & 3u) - 2 * t); // ambiguous (4) hashed as A
+      }
     }
-    amb += __popc(__ballot_sync(0xffffffffu, valid && c == 4 && i >= k)); // only incoming bases, utils.h:113
-    uint32_t v = (valid && c < 4) ? c << (30 - 2 * (i & 15)) : 0u;         // ambiguous hashed as A
-    v |= __shfl_xor_sync(0xffffffffu, v, 8);
-    v |= __shfl_xor_sync(0xffffffffu, v, 4);
-    v |= __shfl_xor_sync(0xffffffffu, v, 2);
     v |= __shfl_xor_sync(0xffffffffu, v, 1);
-    if ((lane & 15) == 0 && (i >> 4) < n_words) pw[i >> 4] = v;
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    if ((lane & 3u) == 0 && (i0 >> 4) < n_words) pw[i0 >> 4] = v;
   }
+  const int amb = (int)__reduce_add_sync(0xffffffffu, amb_lane);
   __syncwarp();
   if (dir == 0) {
     const bool any_noncanon = __any_sync(0xffffffffu, noncanon);
@@ -106,9 +116,9 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
 
   uint8_t status = RS_OK;
   if (n_s <= 0) status = RS_INFEASIBLE;                  // reference: assert, filter.c:167
-  else if (Q > n_s / step) status = RS_EMPTY;            // filter.c:168-172
+  else if (Q * step > n_s) status = RS_EMPTY;            // Q > n_s / step, filter.c:168-172
   else if (amb > A.e) status = RS_EMPTY;                 // filter.c:180-182
-  else if ((n_s - (step - 1)) / step < Q * s) status = RS_INFEASIBLE; // DP table would be < 2 wide
+  else if (n_s - (step - 1) < Q * s * step) status = RS_INFEASIBLE; // (n_s - (step - 1)) / step < Q * s: DP table would be < 2 wide
   uint32_t before = 0, max_f = 0, sum_f = 0;
 
   if (status == RS_OK) {
@@ -123,26 +133,16 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
     }
     __syncwarp();
     bool bad = false; // fewer than Q seeds found: the reference reads uninitialised memory
-    if (A.lane_dp) {
+    // Zero slack (cfg3: 27 seeds per group for 9 x 3): group 0 has the most seeds, so when its table is one column wide
+    // all are, and every selection is forced -- seed r of group g is the group's q-gram (r - 1) * s, read offset
+    // g + (r - 1) * s * step.  No table, no traceback: the sort stage below works out the offsets and the group totals.
+    const bool forced = n_s / step - Q * s + 1 == 1;
+    if (forced) {
+    } else if (A.lane_dp) {
       // ---- one lane per group: serial DP over its own Q x W table -------------------------------
       for (int g = (int)lane; g < step; g += 32) {
         const int n_g = (n_s - g) / step;
         const int W = n_g - Q * s + 1; // real columns 1..W (>= 1 by the feasibility check)
-        if (W == 1) {
-          // zero slack (cfg3: 27 seeds per group for 9 x 3): the table is one column wide and the selection is forced --
-          // seed r is the group's q-gram (r - 1) * s; a row whose sum reaches "infinity" ends the reference's traceback
-          // (column 0), exactly as in the general form below
-          uint32_t sum = 0;
-          for (int r = 1; r <= Q; ++r) {
-            const int q = g + (r - 1) * s * step;
-            uint32_t v = sum + sm_freq[q];
-            if (A.inf <= v) { v = A.inf; bad = true; }
-            sum = v;
-            sel[g * Q + (Q - r)] = (uint16_t)q;
-          }
-          before += sum;
-          continue;
-        }
         uint32_t *M = m_rows + (size_t)g * (w_max + 1);
         uint16_t *am = amin + (size_t)g * Q * w_max;
         for (int c = 0; c <= W; ++c) M[c] = 0; // row 0 (column 0 unused)
@@ -211,29 +211,62 @@ __global__ void __launch_bounds__(128) k_seed(SeedArgs A) {
       before = 0;
     } else {
       // ---- stable ascending sort by frequency inside each group (filter.c:204) and the
-      //      seed tables of the candidate kernel: one lane per (group, seed) ----------------------
+      //      seed tables of the candidate kernel: one lane per (group, seed), whole groups per trip (32 / Q of them) so
+      //      that a lane finds its group's frequencies in its neighbours' registers ----------------------
       uint64_t sum64 = 0;
-      for (int base = 0; base < step * Q; base += 32) {
-        const int idx = base + (int)lane;
-        uint32_t tot = 0;
-        if (idx < step * Q) {
-          const int g = idx / Q, i = idx - g * Q;
-          const uint16_t *sg = sel + g * Q;
-          const uint32_t my_pos = sg[i], f = sm_freq[my_pos];
-          int rank = 0;
-          for (int j = 0; j < Q; ++j) {
-            const uint32_t fj = sm_freq[sg[j]];
-            rank += (fj < f) || (fj == f && j < i);
-            tot += fj;
-          }
+      uint32_t forced_before = 0;
+      const uint32_t gl = lane / (uint32_t)Q, il = lane - gl * (uint32_t)Q, gpt = 32u / (uint32_t)Q; // groups per trip
+      for (uint32_t g0 = 0; g0 < (uint32_t)step; g0 += gpt) {
+        const uint32_t g = g0 + gl;
+        const bool active = gl < gpt && g < (uint32_t)step;
+        uint32_t my_pos = 0, f = 0;
+        if (active) {
+          my_pos = forced ? g + ((uint32_t)Q - 1u - il) * (uint32_t)(s * step) : sel[g * Q + il];
+          f = sm_freq[my_pos];
+        }
+        uint32_t rank = 0, tot = 0;
+        bool wrapped = false;
+        const uint32_t lane0 = gl * (uint32_t)Q; // the group's first lane
+#pragma unroll
+        for (uint32_t j = 0; j < FEM_MAX_Q; ++j) {
+          if (j >= (uint32_t)Q) break;
+          const uint32_t fj = __shfl_sync(0xffffffffu, f, lane0 + j);
+          rank += (fj < f || (fj == f && j < il)) ? 1u : 0u;
+          tot += fj;
+          wrapped |= tot < fj;
+        }
+        if (forced) {
+          // the single column of the reference's table: running sums, "infinity" once one of them reaches it.  They
+          // ascend, so only the total needs the test -- unless a sum wrapped around 2^32 (a q-gram that fills most of a
+          // four-billion-entry index): then the lane walks the column as the reference does, wrap-around included
+          bool bad_g = A.inf <= tot;
+          if (__any_sync(0xffffffffu, active && wrapped)) {
+            if (active && il == 0) {
+              uint32_t sum = 0;
+              bad_g = false;
+              for (int r = 1; r <= Q; ++r) {
+                uint32_t v = sum + sm_freq[g + (uint32_t)(r - 1) * (uint32_t)(s * step)];
+                if (A.inf <= v) { v = A.inf; bad_g = true; }
+                sum = v;
+              }
+              forced_before += sum;
+            }
+          } else if (active && il == 0) forced_before += tot;
+          bad |= active && il == 0 && bad_g;
+        }
+        if (active) {
           const size_t o = ((size_t)rs * step + g) * Q + rank;
           A.seed_begin[o] = sm_begin[my_pos];
           A.seed_freq[o] = f;
           A.seed_start[o] = my_pos;
-          if (i != 0) tot = 0; // one lane per group carries the group's total
         }
+        if (!active || il != 0) tot = 0; // one lane per group carries the group's total
         max_f = max(max_f, __reduce_max_sync(0xffffffffu, tot));
         sum64 += (uint64_t)__reduce_add_sync(0xffffffffu, tot & 0xFFFFu) + ((uint64_t)__reduce_add_sync(0xffffffffu, tot >> 16) << 16);
+      }
+      if (forced) {
+        before = __reduce_add_sync(0xffffffffu, forced_before);
+        if (__any_sync(0xffffffffu, bad)) { status = RS_INFEASIBLE; before = 0; max_f = 0; sum64 = 0; }
       }
       sum_f = sum64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)sum64;
     }

@@ -205,6 +205,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.k = pl.k; sa.step = pl.step; sa.e = pl.e; sa.a = pl.a; sa.Q = pl.Q; sa.s = pl.s;
   sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
   sa.lane_dp = pl.lane_dp;
+  sa.smem_words = (uint32_t)seed_smem_words_per_warp(pl.n_words_max, pl.ns_max, pl.w_max, pl.Q, pl.step, pl.lane_dp);
   sa.codes = s.codes.as<uint8_t>();
   sa.read_flags = s.read_flags.as<uint8_t>();
   sa.rs_status = s.rs_status.as<uint8_t>();

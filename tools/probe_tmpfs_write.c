@@ -10,6 +10,8 @@
  *        G as F, with the pages allocated by a concurrent fallocate thread (4 MB steps) instead of up front
  *        H as E (one mapping, populate per chunk) with the concurrent fallocate thread of G
  *        I as A (one mapping, page faults) with the concurrent fallocate thread
+ *        J as E on the first half of the file (allocated up front) while a fallocate thread allocates the second half:
+ *          do allocator and copiers disturb each other when they are far apart in the file?
  * The file is fallocate'd first in forms A-F (timed separately).
  * gcc -O2 -o /tmp/probe_tmpfs_write tools/probe_tmpfs_write.c -lpthread ; /tmp/probe_tmpfs_write [GB] [threads] [chunk MB] */
 #define _GNU_SOURCE
@@ -47,9 +49,13 @@ static void *coordinator(void *a) {
   }
   return NULL;
 }
+static size_t falloc_from;
+static double falloc_seconds;
 static void *falloc_thread(void *a) {
   (void)a;
-  for (size_t o = 0; o < S; o += 4u << 20) if (fallocate(fd, FALLOC_FL_KEEP_SIZE, (off_t)o, 4 << 20)) { perror("fallocate"); break; }
+  const double t0 = now();
+  for (size_t o = falloc_from; o < S; o += 4u << 20) if (fallocate(fd, FALLOC_FL_KEEP_SIZE, (off_t)o, 4 << 20)) { perror("fallocate"); break; }
+  falloc_seconds = now() - t0;
   return NULL;
 }
 static void *work_f(void *a) {
@@ -74,7 +80,7 @@ static void *work(void *a) {
   (void)a;
   for (;;) {
     const size_t c = __sync_fetch_and_add(&next_chunk, 1), off = c * CH;
-    if (off >= S) break;
+    if (off >= (form == 'J' ? S / 2 : S)) break;
     const size_t n = CH < S - off ? CH : S - off;
     if (form == 'A' || form == 'I') memcpy(shared_map + off, src + off, n);
     else if (form == 'B' || form == 'C') {
@@ -85,7 +91,7 @@ static void *work(void *a) {
     } else if (form == 'D') {
       size_t done = 0;
       while (done < n) { const ssize_t w = pwrite(fd, src + off + done, n - done, (off_t)(off + done)); if (w <= 0) { perror("pwrite"); exit(1); } done += (size_t)w; }
-    } else if (form == 'E' || form == 'H') {
+    } else if (form == 'E' || form == 'H' || form == 'J') {
       madvise(shared_map + off, n, MADV_POPULATE_WRITE);
       memcpy(shared_map + off, src + off, n);
     }
@@ -106,11 +112,13 @@ int main(int argc, char **argv) {
     fd = open(path, O_RDWR | O_CREAT | O_TRUNC, 0644);
     if (fd < 0 || ftruncate(fd, (off_t)S)) { perror("file"); return 1; }
     double t0 = now();
-    const int concurrent = form == 'G' || form == 'H' || form == 'I', batched = form == 'F' || form == 'G';
+    const int concurrent = form == 'G' || form == 'H' || form == 'I' || form == 'J', batched = form == 'F' || form == 'G';
     if (!concurrent && fallocate(fd, 0, 0, (off_t)S)) perror("fallocate");
+    falloc_from = 0;
+    if (form == 'J') { if (fallocate(fd, 0, 0, (off_t)(S / 2))) perror("fallocate"); falloc_from = S / 2; }
     const double tf = now() - t0 + 1e-9;
     shared_map = NULL;
-    if (form == 'A' || form == 'E' || form == 'H' || form == 'I') shared_map = mmap(NULL, S, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (form == 'A' || form == 'E' || form == 'H' || form == 'I' || form == 'J') shared_map = mmap(NULL, S, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
     next_chunk = 0;
     pthread_t th[64], tc, tfa;
     if (batched) {
@@ -125,6 +133,7 @@ int main(int argc, char **argv) {
     if (batched) pthread_create(&tc, NULL, coordinator, NULL);
     for (int i = 0; i < T; ++i) pthread_create(&th[i], NULL, batched ? work_f : work, NULL);
     for (int i = 0; i < T; ++i) pthread_join(th[i], NULL);
+    const double tcopy = now() - t0;
     if (batched) { pthread_join(tc, NULL); free(fb); }
     if (concurrent) pthread_join(tfa, NULL);
     const double tw = now() - t0;
@@ -132,6 +141,8 @@ int main(int argc, char **argv) {
     if (shared_map) munmap(shared_map, S);
     const double tu = now() - t0;
     printf("form %c, %d threads, %zu MB chunks: fallocate %.1f GB/s, copies %.3f s = %.1f GB/s, munmap %.3f s\n", form, T, CH >> 20, S / tf / 1e9, tw, S / tw / 1e9, tu);
+    if (concurrent) printf("        copiers alone %.3f s for %.1f GB = %.1f GB/s; concurrent fallocate %.3f s for %.1f GB = %.1f GB/s\n", tcopy, (form == 'J' ? S / 2 : S) / 1e9,
+                           (form == 'J' ? S / 2 : S) / tcopy / 1e9, falloc_seconds, (S - falloc_from) / 1e9, (S - falloc_from) / falloc_seconds / 1e9);
     close(fd);
     unlink(path);
   }
