@@ -168,6 +168,7 @@ struct femgpu_ctx {
   size_t smem_optin = 0;
   // index
   DBuf lut, occ;
+  DBuf base_table;     // k_seed: code and flags of every byte value, both strands (seed_base_table)
   uint64_t n_occ = 0;
   int idx_k = 0, idx_step = 0;
   // reference
@@ -238,6 +239,15 @@ extern "C" femgpu_ctx *femgpu_create(int device) {
     for (auto &e : s.ev) cudaEventCreate(&e);
     cudaEventCreateWithFlags(&s.ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
   }
+  {
+    uint8_t table[SEED_TABLE_BYTES];
+    seed_base_table(table);
+    if (c->base_table.reserve(SEED_TABLE_BYTES) || cudaMemcpy(c->base_table.p, table, SEED_TABLE_BYTES, cudaMemcpyHostToDevice) != cudaSuccess) {
+      set_error(FEMGPU_ECUDA, "base table upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+      femgpu_destroy(c);
+      return nullptr;
+    }
+  }
   return c;
 }
 
@@ -261,7 +271,7 @@ extern "C" void femgpu_destroy(femgpu_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto &s : c->slot) slot_release(s);
-  c->lut.release(); c->occ.release(); c->ref2.release(); c->refn.release(); c->refp0.release(); c->refp1.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
+  c->lut.release(); c->occ.release(); c->base_table.release(); c->ref2.release(); c->refn.release(); c->refp0.release(); c->refp1.release(); c->rec_base.release(); c->rec_len.release(); c->rnames.release(); c->rname_off.release();
   delete c;
 }
 

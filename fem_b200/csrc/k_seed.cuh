@@ -22,6 +22,7 @@ struct SeedArgs {
   const uint64_t *read_off;   // n_reads + 1
   uint32_t n_reads;
   const uint32_t *lut;
+  const uint8_t *base_table;  // [strand][byte]: code (0..4, complemented on strand 1) | 8 if the byte is none of "ACGTN" (seed_base_table)
   uint32_t inf;               // (uint32) occurrence_table_size: the DP's "infinity" (filter.c:9)
   int k, step, e, a, Q, s;
   int n_words_max, ns_max, w_max; // shared-memory plan for the longest read of the batch
@@ -48,13 +49,32 @@ __host__ __device__ inline size_t seed_smem_words_per_warp(int n_words_max, int 
          ((size_t)step * Q + 1) / 2;
 }
 
+#define SEED_TABLE_BYTES 512 // shared-memory copy of base_table, after the four warps' areas
+
+// src/utils.h:72 (codes) and src/sequence_batch.h:96 (complement of strand 1) for every byte value, plus the "not one
+// of ACGTN in upper case" flag that sends a read's SAM text to the host
+inline void seed_base_table(uint8_t out[SEED_TABLE_BYTES]) {
+  for (int d = 0; d < 2; ++d)
+    for (int ch = 0; ch < 256; ++ch) {
+      uint32_t c = fem_base_code((unsigned char)ch);
+      if (d && c < 4) c = 3u - c;
+      const bool canon = ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T' || ch == 'N';
+      out[d * 256 + ch] = (uint8_t)(c | (canon ? 0u : 8u));
+    }
+}
+
+template <int QT>
 __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   extern __shared__ uint32_t smem_seed[];
   const uint32_t lane = lane_id();
   const uint32_t warp_in_block = threadIdx.x >> 5;
+  uint8_t *tbl = reinterpret_cast<uint8_t *>(smem_seed + 4u * A.smem_words);
+  reinterpret_cast<uint32_t *>(tbl)[threadIdx.x] = __ldg(reinterpret_cast<const uint32_t *>(A.base_table) + threadIdx.x); // 128 x 4 bytes
+  __syncthreads();
   const uint64_t rs = (uint64_t)blockIdx.x * (blockDim.x >> 5) + warp_in_block;
   if (rs >= 2ull * A.n_reads) return;
-  const int k = A.k, step = A.step, Q = A.Q, s = A.s, w_max = A.w_max;
+  const int k = A.k, step = A.step, s = A.s, w_max = A.w_max;
+  constexpr int Q = QT;
   const uint32_t groups = A.lane_dp ? (uint32_t)step : 1u;
   uint32_t *pw = smem_seed + warp_in_block * A.smem_words;  // 2-bit packed read, big-endian in word
   uint32_t *sm_freq = pw + A.n_words_max;
@@ -77,36 +97,44 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   }
 
   // ---- base codes (strand oriented), 2-bit packing, ambiguous-base count --------------------
-  // Four consecutive bases per lane and trip (128 bases per trip: a 150 bp read takes two).  A byte ch is a letter of
-  // "ACGT" in either case iff x = ch ^ 0x40 without its case bit is < 32 and bit x of ACGT_MASK is set (A 1, C 3, G 7,
-  // T 20); its code (src/utils.h:72) is then ((ch >> 1) ^ (ch >> 2)) & 3 -- A 0, C 1, G 2, T 3 -- and 4 otherwise.
-  constexpr uint32_t ACGT_MASK = (1u << 1) | (1u << 3) | (1u << 7) | (1u << 20), ACGTN_MASK = ACGT_MASK | (1u << 14);
-  uint32_t amb_lane = 0;
-  bool noncanon = false;
+  // Four consecutive characters per lane and trip (128 per trip: a 150 bp read takes two), fetched as the two aligned
+  // words that hold them; on strand 1 they are the four that END at l - 1 - i0, byte-reversed.  Each goes through the
+  // 256-entry table once; the four entries side by side in one register give the codes (stored as one word when the
+  // destination is aligned), the 2-bit packing, the ambiguous count and the "not ACGTN" flag without per-character work.
+  uint32_t amb_lane = 0, flags = 0;
   const int n_words = (l + 15) / 16 + 1;
-  const char *rb = A.bases + off;
+  const uint32_t *bw = reinterpret_cast<const uint32_t *>(A.bases);
+  const uint8_t *tb = tbl + 256u * dir;
+  const bool word_stores = ((2 * off + (uint64_t)dir * (uint64_t)l) & 3u) == 0;
   for (int base = 0; base < n_words * 16; base += 128) {
     const int i0 = base + 4 * (int)lane;
-    uint32_t v = 0;
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const int i = i0 + t;
-      if (i < l) {
-        const uint32_t ch = (unsigned char)(dir ? rb[l - 1 - i] : rb[i]);
-        const uint32_t x = ch ^ 0x40u;
-        const bool acgt = (x & 0xDFu) < 32u && ((ACGT_MASK >> (x & 31u)) & 1u);
-        noncanon |= !(x < 32u && ((ACGTN_MASK >> (x & 31u)) & 1u)); // anything but upper-case "ACGTN"
-        uint32_t c = ((ch >> 1) ^ (ch >> 2)) & 3u;
-        if (dir) c ^= 3u;                        // complement; ambiguous stays ambiguous (-> 'N')
-        if (!acgt) { c = 4u; amb_lane += i >= k; } // only incoming bases count, utils.h:113
-        codes[i] = (uint8_t)c;
-        v |= (c & 3u) << (30 - 8 * (int)(lane & 3u) - 2 * t); // ambiguous (4) hashed as A
-      }
+    uint32_t E = 0;
+    const int nvalid = min(max(l - i0, 0), 4);
+    if (nvalid > 0) {
+      const int64_t sb = (int64_t)off + (dir ? l - 4 - i0 : i0); // first byte of the four; >= -3
+      const int64_t wi = sb >> 2;
+      const uint32_t w0 = wi >= 0 ? __ldg(bw + wi) : 0u, w1 = __ldg(bw + wi + 1); // the buffer ends 16 bytes after the last base
+      uint32_t x = __funnelshift_r(w0, w1, ((uint32_t)sb & 3u) * 8u);
+      if (dir) x = __byte_perm(x, 0u, 0x0123);
+      if (nvalid < 4) { const uint32_t m = (1u << (8 * nvalid)) - 1u; x = (x & m) | (0x41414141u & ~m); } // past the end: 'A'
+      E = (uint32_t)tb[x & 0xFFu] | ((uint32_t)tb[(x >> 8) & 0xFFu] << 8) | ((uint32_t)tb[(x >> 16) & 0xFFu] << 16) | ((uint32_t)tb[x >> 24] << 24);
+      flags |= E;
+      // ambiguous incoming bases (utils.h:113): code 4 = bit 2 of the entry, characters i >= k only
+      uint32_t a4 = E & 0x04040404u;
+      if (i0 < k) a4 = k - i0 >= 4 ? 0u : a4 & ~((1u << (8 * (k - i0))) - 1u);
+      amb_lane += __popc(a4);
+      const uint32_t cw = E & 0x07070707u;
+      if (word_stores && nvalid == 4) *reinterpret_cast<uint32_t *>(codes + i0) = cw;
+      else
+        for (int t = 0; t < nvalid; ++t) codes[i0 + t] = (uint8_t)(cw >> (8 * t));
     }
+    const uint32_t t1 = E & 0x03030303u; // ambiguous (4) hashed as A
+    uint32_t v = (((t1 << 6) | (t1 >> 4) | (t1 >> 14) | (t1 >> 24)) & 0xFFu) << (24 - 8 * (int)(lane & 3u));
     v |= __shfl_xor_sync(0xffffffffu, v, 1);
     v |= __shfl_xor_sync(0xffffffffu, v, 2);
     if ((lane & 3u) == 0 && (i0 >> 4) < n_words) pw[i0 >> 4] = v;
   }
+  const bool noncanon = (flags & 0x08080808u) != 0;
   const int amb = (int)__reduce_add_sync(0xffffffffu, amb_lane);
   __syncwarp();
   if (dir == 0) {
@@ -136,7 +164,7 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
     // Zero slack (cfg3: 27 seeds per group for 9 x 3): group 0 has the most seeds, so when its table is one column wide
     // all are, and every selection is forced -- seed r of group g is the group's q-gram (r - 1) * s, read offset
     // g + (r - 1) * s * step.  No table, no traceback: the sort stage below works out the offsets and the group totals.
-    const bool forced = n_s / step - Q * s + 1 == 1;
+    const bool forced = Q * s * step <= n_s && n_s < (Q * s + 1) * step; // n_s / step - Q * s + 1 == 1
     if (forced) {
     } else if (A.lane_dp) {
       // ---- one lane per group: serial DP over its own Q x W table -------------------------------
@@ -224,17 +252,16 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
           my_pos = forced ? g + ((uint32_t)Q - 1u - il) * (uint32_t)(s * step) : sel[g * Q + il];
           f = sm_freq[my_pos];
         }
-        uint32_t rank = 0, tot = 0;
-        bool wrapped = false;
+        uint32_t rank = 0, tot = 0, fmx = 0;
         const uint32_t lane0 = gl * (uint32_t)Q; // the group's first lane
 #pragma unroll
-        for (uint32_t j = 0; j < FEM_MAX_Q; ++j) {
-          if (j >= (uint32_t)Q) break;
+        for (uint32_t j = 0; j < (uint32_t)Q; ++j) {
           const uint32_t fj = __shfl_sync(0xffffffffu, f, lane0 + j);
           rank += (fj < f || (fj == f && j < il)) ? 1u : 0u;
           tot += fj;
-          wrapped |= tot < fj;
+          fmx = max(fmx, fj);
         }
+        const bool wrapped = fmx > 0xFFFFFFFFu / (uint32_t)Q; // else the sums of Q frequencies cannot pass 2^32
         if (forced) {
           // the single column of the reference's table: running sums, "infinity" once one of them reaches it.  They
           // ascend, so only the total needs the test -- unless a sum wrapped around 2^32 (a q-gram that fills most of a

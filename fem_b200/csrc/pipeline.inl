@@ -45,7 +45,7 @@ static int make_plan(femgpu_ctx *c, const femgpu_params *p, int l_max, Plan *pl,
   pl->w_max = std::max(pl->ns_max / pl->step - pl->Q * pl->s + 1, 1);
   // one lane per group pays Q*W serial steps, the warp scan pays step*Q*ceil(W/32) rounds of ~7x the cost
   pl->lane_dp = c->seed_dp_mode == 1 ? 1 : c->seed_dp_mode == 2 ? 0 : pl->w_max <= 8 * pl->step;
-  pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4; // 4 warps
+  pl->seed_smem = 4 * seed_smem_words_per_warp(pl->n_words_max, pl->ns_max, pl->w_max, pl->Q, pl->step, pl->lane_dp) * 4 + SEED_TABLE_BYTES; // 4 warps + the base table
   // several read-strands per warp where the lane form leaves most lanes idle (k_seed_multi.cuh).  Automatic
   // choice: only while the lookup table stays in L2 (k <= 12, 67 MB; with k = 14 its gathers go to HBM and the
   // one-read-strand form's larger number of warps in flight wins: cfg5 10 ms against 22 ms) and while the
@@ -201,6 +201,7 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.read_off = s.read_off.as<uint64_t>();
   sa.n_reads = n_reads;
   sa.lut = c->lut.as<uint32_t>();
+  sa.base_table = c->base_table.as<uint8_t>();
   sa.inf = (uint32_t)c->n_occ;
   sa.k = pl.k; sa.step = pl.step; sa.e = pl.e; sa.a = pl.a; sa.Q = pl.Q; sa.s = pl.s;
   sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
@@ -236,8 +237,17 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
     const uint64_t per_block = 4ull * (uint64_t)pl.seed_R;
     k_seed_multi<<<(unsigned)((n_rs + per_block - 1) / per_block), 128, pl.seed_smem, s.stream>>>(sm);
   } else {
-    if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem));
-    k_seed<<<(unsigned)((n_rs + 3) / 4), 128, pl.seed_smem, s.stream>>>(sa);
+#define FEM_SEED_LAUNCH(QT)                                                                                                          \
+  case QT:                                                                                                                         \
+    if (pl.seed_smem > 48 * 1024) CU(cudaFuncSetAttribute(k_seed<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.seed_smem)); \
+    k_seed<QT><<<(unsigned)((n_rs + 3) / 4), 128, pl.seed_smem, s.stream>>>(sa);                                                  \
+    break;
+    switch (pl.Q) { // Q = e + 1 + a seeds per group, a compile-time constant of the kernel
+      FEM_SEED_LAUNCH(1) FEM_SEED_LAUNCH(2) FEM_SEED_LAUNCH(3) FEM_SEED_LAUNCH(4) FEM_SEED_LAUNCH(5)
+      FEM_SEED_LAUNCH(6) FEM_SEED_LAUNCH(7) FEM_SEED_LAUNCH(8) FEM_SEED_LAUNCH(9) FEM_SEED_LAUNCH(10)
+      default: return set_error(FEMGPU_EINVAL, "Q = %d seeds per group outside 1..%d", pl.Q, FEM_MAX_Q);
+    }
+#undef FEM_SEED_LAUNCH
   }
   ++s.n_launches;
   CU(cudaGetLastError());
