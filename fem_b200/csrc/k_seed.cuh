@@ -28,6 +28,7 @@ struct SeedArgs {
   int n_words_max, ns_max, w_max; // shared-memory plan for the longest read of the batch
   int lane_dp;
   uint32_t smem_words;        // seed_smem_words_per_warp of this plan
+  uint32_t amin_word, sel_word; // word offsets of the arg-min tables and the selected positions in a warp's area
   uint8_t *codes;             // out: 2 * total_bases; strand d of read i at 2*off[i] + d*len
   uint8_t *read_flags;        // out: per read, bit 0 = a character outside "ACGTN" (k_trace leaves it to the host)
   uint8_t *rs_status;         // out: per read-strand
@@ -75,13 +76,12 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   if (rs >= 2ull * A.n_reads) return;
   const int k = A.k, step = A.step, s = A.s, w_max = A.w_max;
   constexpr int Q = QT;
-  const uint32_t groups = A.lane_dp ? (uint32_t)step : 1u;
   uint32_t *pw = smem_seed + warp_in_block * A.smem_words;  // 2-bit packed read, big-endian in word
   uint32_t *sm_freq = pw + A.n_words_max;
   uint32_t *sm_begin = sm_freq + A.ns_max;
   uint32_t *m_rows = sm_begin + A.ns_max;                   // [groups][w_max + 1], columns 0..W
-  uint16_t *amin = reinterpret_cast<uint16_t *>(m_rows + groups * (w_max + 1)); // [groups][Q][w_max]
-  uint16_t *sel = reinterpret_cast<uint16_t *>(m_rows + groups * (w_max + 1) + (groups * Q * w_max + 1) / 2); // [step][Q]
+  uint16_t *amin = reinterpret_cast<uint16_t *>(pw + A.amin_word); // [groups][Q][w_max]
+  uint16_t *sel = reinterpret_cast<uint16_t *>(pw + A.sel_word);   // [step][Q]
 
   const uint32_t read = (uint32_t)(rs >> 1), dir = (uint32_t)(rs & 1);
   const uint64_t off = A.read_off[read];
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   const int n_words = (l + 15) / 16 + 1;
   const uint32_t *bw = reinterpret_cast<const uint32_t *>(A.bases);
   const uint8_t *tb = tbl + 256u * dir;
-  const bool word_stores = ((2 * off + (uint64_t)dir * (uint64_t)l) & 3u) == 0;
+  const uint32_t store_align = (uint32_t)(2 * off + (uint64_t)dir * (uint64_t)l) & 3u; // of codes + i0: the same for every lane
   for (int base = 0; base < n_words * 16; base += 128) {
     const int i0 = base + 4 * (int)lane;
     uint32_t E = 0;
@@ -124,8 +124,15 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
       if (i0 < k) a4 = k - i0 >= 4 ? 0u : a4 & ~((1u << (8 * (k - i0))) - 1u);
       amb_lane += __popc(a4);
       const uint32_t cw = E & 0x07070707u;
-      if (word_stores && nvalid == 4) *reinterpret_cast<uint32_t *>(codes + i0) = cw;
-      else
+      if (nvalid == 4 && store_align == 0) *reinterpret_cast<uint32_t *>(codes + i0) = cw;
+      else if (nvalid == 4 && store_align == 2) {
+        *reinterpret_cast<uint16_t *>(codes + i0) = (uint16_t)cw;
+        *reinterpret_cast<uint16_t *>(codes + i0 + 2) = (uint16_t)(cw >> 16);
+      } else if (nvalid == 4) {
+        codes[i0] = (uint8_t)cw;
+        *reinterpret_cast<uint16_t *>(codes + i0 + 1) = (uint16_t)(cw >> 8);
+        codes[i0 + 3] = (uint8_t)(cw >> 24);
+      } else
         for (int t = 0; t < nvalid; ++t) codes[i0 + t] = (uint8_t)(cw >> (8 * t));
     }
     const uint32_t t1 = E & 0x03030303u; // ambiguous (4) hashed as A
@@ -152,12 +159,24 @@ __global__ void __launch_bounds__(128, 12) k_seed(SeedArgs A) {
   if (status == RS_OK) {
     // ---- hashes and lookup-table gathers (two adjacent uint32 per q-gram) --------------------
     const uint32_t mask = (uint32_t)((1ull << (2 * k)) - 1);
-    for (int p = (int)lane; p < n_s; p += 32) {
-      const uint64_t x = ((uint64_t)pw[p >> 4] << 32) | pw[(p >> 4) + 1];
-      const uint32_t h = (uint32_t)(x >> (64 - 2 * (p & 15) - 2 * k)) & mask;
-      const uint32_t b = __ldg(A.lut + h), e2 = __ldg(A.lut + h + 1);
-      sm_begin[p] = b;
-      sm_freq[p] = e2 - b;
+    for (int p0 = (int)lane; p0 < n_s; p0 += 128) { // four q-grams per lane with their eight loads in flight together
+      uint32_t b[4], e2[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int p = p0 + 32 * u;
+        b[u] = e2[u] = 0;
+        if (p < n_s) {
+          const uint64_t x = ((uint64_t)pw[p >> 4] << 32) | pw[(p >> 4) + 1];
+          const uint32_t h = (uint32_t)(x >> (64 - 2 * (p & 15) - 2 * k)) & mask;
+          b[u] = __ldg(A.lut + h);
+          e2[u] = __ldg(A.lut + h + 1);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int p = p0 + 32 * u;
+        if (p < n_s) { sm_begin[p] = b[u]; sm_freq[p] = e2[u] - b[u]; }
+      }
     }
     __syncwarp();
     bool bad = false; // fewer than Q seeds found: the reference reads uninitialised memory

@@ -207,6 +207,11 @@ static int run_seed_and_candidates(femgpu_ctx *c, Slot &s, const Plan &pl) {
   sa.n_words_max = pl.n_words_max; sa.ns_max = pl.ns_max; sa.w_max = pl.w_max;
   sa.lane_dp = pl.lane_dp;
   sa.smem_words = (uint32_t)seed_smem_words_per_warp(pl.n_words_max, pl.ns_max, pl.w_max, pl.Q, pl.step, pl.lane_dp);
+  {
+    const uint32_t groups = pl.lane_dp ? (uint32_t)pl.step : 1u;
+    sa.amin_word = (uint32_t)pl.n_words_max + 2u * (uint32_t)pl.ns_max + groups * (uint32_t)(pl.w_max + 1);
+    sa.sel_word = sa.amin_word + (groups * (uint32_t)pl.Q * (uint32_t)pl.w_max + 1u) / 2u;
+  }
   sa.codes = s.codes.as<uint8_t>();
   sa.read_flags = s.read_flags.as<uint8_t>();
   sa.rs_status = s.rs_status.as<uint8_t>();
