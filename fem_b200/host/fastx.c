@@ -236,10 +236,18 @@ int femhost_parse_fastq4(const unsigned char *p, const unsigned char *end, femho
   out->n_bases = 0;
   if (femhost_records_reserve(out, 1, 16, 16)) return -3;
   int oom = 0;
+  const unsigned char *first = p;
   while (p < end) {
     const unsigned char *next = fastq4_record(p, end, out, &oom);
     if (!next) return oom ? -3 : 1;
     ++out->n_records;
+    if (p == first && next < end) {
+      /* room for the whole buffer at once, from the first record's shape (reads of one run look alike): the arrays are
+       * pinned, and growing them by doubling costs an allocation, a copy and a release of pinned memory each time */
+      const size_t rec = (size_t)(next - first), est = (size_t)(end - first) / rec + 64;
+      const size_t nb = (size_t)out->base_off[1] + 1, nn = (size_t)out->name_off[1] + 1;
+      if (femhost_records_reserve(out, est, est * nb + est * nb / 32, est * nn + est * nn / 4)) return -3;
+    }
     p = next;
   }
   out->n_bases = out->base_off[out->n_records];
