@@ -72,15 +72,6 @@ probe)
   timeout 1200 ncu --set full --clock-control none -k regex:'k_int_peak' -c 6 \
     -o $out/${tag}_probe -f python bench.py $small > $out/${tag}_ncu_probe.log 2>&1; echo "ncu probe rc=$?" ;;
 e2etune)
-  d=$(ls -d /tmp/fem_bench/ref3100000000_rec24_rep0_seed3 2>/dev/null)
-  if [ -z "$d" ]; then python bench.py --steps 1 --warmup 3 --no-cpu-baseline --e2e-steps 1 --others none > /dev/null 2>&1; d=/tmp/fem_bench/ref3100000000_rec24_rep0_seed3; fi
-  fq=$(ls $d/reads_10000000_*.fq | head -1)
-  for v in "X=0" "FEM_SAM_COPIERS=10" "FEM_SAM_COPIERS=14" "FEM_READERS=8 FEM_SAM_COPIERS=10" "FEM_SAM_PREALLOC=0" "FEM_SAM_MMAP=0" "FEM_SAM_POPULATE=0" $TUNES; do
-    for rep in 1 2; do
-      rm -f /dev/shm/tune.sam
-      env $v fem_b200/bin/FEM map -e 7 -t 13 --ref $d/ref.fa --index $d/index_k12_s5 --read1 $fq -o /dev/shm/tune.sam 2>&1 | grep -E "^Time|phases" | tr '\n' ' '; echo " [$v]"
-    done
-  done 2>&1 | tee $out/${tag}_e2etune.txt
-  rm -f /dev/shm/tune.sam ;;
+  bash tools/e2e_tune.sh $tag "FEM_SAM_COPIERS=10" "FEM_READERS=8 FEM_SAM_COPIERS=10" "FEM_SAM_PREALLOC=0" "FEM_SAM_MMAP=0" "FEM_SAM_POPULATE=0" $TUNES ;;
 esac; done
 ls -la $out | tail -20
