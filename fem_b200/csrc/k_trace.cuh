@@ -162,7 +162,10 @@ __device__ uint32_t md_build_store_planes(const uint32_t *rp0, const uint32_t *r
 }
 
 template <bool HAS_N, int LCAP>
-__global__ void __launch_bounds__(128) k_trace(TraceArgs A) {
+// 12 blocks per SM (40 registers, 20 bytes of spills): the kernel waits on its history words in local memory (ncu: 12 stall
+// cycles per instruction on loads at 48 registers and 10 blocks), so more resident warps pay -- cfg3 1.19 -> 1.04 ms per 1 M
+// reads, cfg2 0.73 -> 0.65, cfg5 1.82 -> 1.57; 16 blocks (32 registers, 64 bytes of spills) 1.21.
+__global__ void __launch_bounds__(128, 12) k_trace(TraceArgs A) {
   const uint64_t mi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (mi >= A.n_maps) return;
   uint32_t *out = A.aln + mi * ALN_WORDS;
